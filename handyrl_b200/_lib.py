@@ -1,0 +1,90 @@
+"""ctypes binding of libb200rl.so (C-ABI declared in include/b200rl.h).
+
+The library is built in-tree by `make -C handyrl_b200/csrc` (or
+`__graft_entry__.build()`).  Loading fails loudly when it is missing: the
+product has no CPU or eager-PyTorch fallback.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200rl.so")
+
+_lib = None
+
+c_i64 = ctypes.c_int64
+c_int = ctypes.c_int
+c_ptr = ctypes.c_void_p
+c_dbl = ctypes.c_double
+c_u64 = ctypes.c_uint64
+
+
+class B200RLError(RuntimeError):
+    pass
+
+
+def _view3():
+    return [c_ptr, c_i64, c_i64, c_i64]
+
+
+_SCAN_TAIL = (
+    _view3()                      # values
+    + [c_ptr, c_i64, c_i64]       # boot
+    + _view3()                    # rewards
+    + _view3()                    # rhos
+    + _view3()                    # cs
+    + [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_dbl, c_dbl, c_ptr]
+)
+
+# name -> argtypes; restype is int except where noted.  Must list every symbol
+# include/b200rl.h declares (tests/test_abi.py checks this against the header).
+SIGNATURES = {
+    "b200rl_version": [],
+    "b200rl_target_scan": [c_int] + _SCAN_TAIL,
+    "b200rl_target_scan_fused": [c_int, c_int] + _SCAN_TAIL,
+    "b200rl_target_mc": _view3() + _view3() + [c_ptr, c_i64, c_i64, c_i64, c_ptr],
+}
+
+
+def lib():
+    """Load (once) and return the ctypes handle of libb200rl.so."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B200RLError(
+            "libb200rl.so not found at %s — build it with `make -C handyrl_b200/csrc` "
+            "(there is no CPU fallback)" % LIB_PATH
+        )
+    h = ctypes.CDLL(LIB_PATH)
+    h.b200rl_last_error.restype = ctypes.c_char_p
+    h.b200rl_last_error.argtypes = []
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(h, name)
+        fn.argtypes = argtypes
+        fn.restype = c_int
+    _lib = h
+    return h
+
+
+def check(status, what=""):
+    if status != 0:
+        msg = lib().b200rl_last_error()
+        raise B200RLError("%s failed (%d): %s" % (what, status, msg.decode() if msg else "?"))
+
+
+def call(name, *args):
+    check(getattr(lib(), name)(*args), name)
+
+
+def stream_ptr():
+    import torch
+
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def require_cuda(t, name):
+    if not t.is_cuda:
+        raise B200RLError(
+            "%s must be a CUDA tensor: handyrl_b200 runs only on the GPU (no CPU fallback)" % name
+        )

@@ -1,0 +1,70 @@
+// Shared helpers for the b200rl CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#define B200RL_OK 0
+#define B200RL_ERR_ARG 1
+#define B200RL_ERR_CUDA 2
+#define B200RL_ERR_UNSUPPORTED 3
+
+// Thread-local last-error message, read through b200rl_last_error().
+void b200rl_set_error(const char* fmt, ...);
+
+static inline int b200rl_check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        b200rl_set_error("%s: %s", what, cudaGetErrorString(e));
+        return B200RL_ERR_CUDA;
+    }
+    return B200RL_OK;
+}
+
+#define B200RL_REQUIRE(cond, ...)            \
+    do {                                     \
+        if (!(cond)) {                       \
+            b200rl_set_error(__VA_ARGS__);   \
+            return B200RL_ERR_ARG;           \
+        }                                    \
+    } while (0)
+
+// 128-bit streaming store: output tensors are written once and consumed by a
+// later kernel (the net / the loss), so do not allocate them in L1.
+__device__ __forceinline__ void st_stream_f4(float4* p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+__device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ uint4 ld_stream_u4(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+// Counter-based RNG: splitmix64 finaliser over (seed, stream id, counter).
+// Used for the device-side uniform policy and ParallelTicTacToe's selected player;
+// parity with the reference is defined on action tapes, never on RNG streams.
+__host__ __device__ __forceinline__ uint64_t b200rl_mix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__host__ __device__ __forceinline__ uint32_t b200rl_rand32(uint64_t seed, uint64_t stream, uint64_t counter) {
+    uint64_t h = b200rl_mix64(seed ^ b200rl_mix64(stream * 0xD6E8FEB86659FD93ull + counter));
+    return (uint32_t)(h >> 32);
+}

@@ -1,0 +1,49 @@
+"""CPU: libb200rl.so loads and exports every symbol include/b200rl.h declares."""
+import ctypes
+import os
+import re
+
+from handyrl_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "b200rl.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200rl_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    syms = _declared_symbols()
+    assert len(syms) >= 4
+    h = ctypes.CDLL(_lib.LIB_PATH)
+    for s in syms:
+        assert hasattr(h, s), "libb200rl.so does not export %s" % s
+
+
+def test_python_binding_covers_header():
+    syms = set(_declared_symbols()) - {"b200rl_last_error"}
+    assert syms == set(_lib.SIGNATURES), (syms ^ set(_lib.SIGNATURES))
+
+
+def test_version_and_error_string():
+    h = _lib.lib()
+    assert h.b200rl_version() >= 1
+    assert isinstance(h.b200rl_last_error(), bytes)
+
+
+def test_argument_errors_do_not_need_a_gpu():
+    h = _lib.lib()
+    z = ctypes.c_void_p(0)
+    st = h.b200rl_target_mc(z, 0, 0, 0, z, 0, 0, 0, z, 1, 1, 1, z)
+    assert st != 0 and b"null" in h.b200rl_last_error()
+
+
+def test_no_cpu_fallback():
+    import pytest
+    import torch
+    from handyrl_b200.losses import compute_target
+    v = torch.zeros(2, 3, 2, 1)
+    with pytest.raises(_lib.B200RLError):
+        compute_target('TD', v, v, None, 0.7, 1.0, None, None)
