@@ -43,7 +43,21 @@ SIGNATURES = {
     "b200rl_target_scan": [c_int] + _SCAN_TAIL,
     "b200rl_target_scan_fused": [c_int, c_int] + _SCAN_TAIL,
     "b200rl_target_mc": _view3() + _view3() + [c_ptr, c_i64, c_i64, c_i64, c_ptr],
+    "b200rl_env_state_bytes": [c_int],
+    "b200rl_env_dims": [c_int, c_ptr],
+    "b200rl_env_reset": [c_int, c_ptr, c_i64, c_ptr, c_ptr],
+    "b200rl_env_step": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+    "b200rl_env_legal_list": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
+    "b200rl_env_observe": [c_int, c_ptr, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+    "b200rl_env_outcome": [c_int, c_ptr, c_i64, c_ptr, c_ptr],
+    "b200rl_env_info": [c_int, c_ptr, c_i64, c_ptr, c_ptr],
+    "b200rl_env_step_observe": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_int] + [c_ptr] * 8,
+    "b200rl_env_rollout": [c_int, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
+                           c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr],
 }
+
+# functions that return a value instead of a status
+_RESTYPE = {"b200rl_env_state_bytes": c_i64}
 
 
 def lib():
@@ -62,7 +76,7 @@ def lib():
     for name, argtypes in SIGNATURES.items():
         fn = getattr(h, name)
         fn.argtypes = argtypes
-        fn.restype = c_int
+        fn.restype = _RESTYPE.get(name, c_int)
     _lib = h
     return h
 

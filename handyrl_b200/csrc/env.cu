@@ -1,0 +1,439 @@
+// Batched game engine kernels: one game per thread, 32 games per warp tile.
+//
+// Replaces, for N concurrent games, the per-game Python calls of the reference
+// `Environment` interface (handyrl/environment.py:43-146) and the body of the
+// self-play loop that drives it (handyrl/generation.py:31-68).
+#include "common.cuh"
+#include "games.cuh"
+#include "emit.cuh"
+#include "../../include/b200rl.h"
+
+namespace {
+
+constexpr int BLK = 128;           // threads per CTA = games per CTA
+constexpr int WARPS = BLK / 32;
+
+// shared staging per warp: observation bits, legal bits, scalar bits for 32 games
+template <class G>
+struct WarpStage {
+    uint32_t obs[32 * G::OW];
+    uint32_t legal[32 * G::LW];
+    uint32_t scalar[32];
+};
+
+template <class G>
+__global__ void __launch_bounds__(BLK) k_reset(uint32_t* state, int64_t N, const uint8_t* __restrict__ mask) {
+    int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
+    if (i >= N) return;
+    if (mask && !mask[i]) return;
+    typename G::State s;
+    G::reset(s);
+    G::store(state, N, i, s);
+}
+
+template <class G>
+__global__ void __launch_bounds__(BLK) k_step(uint32_t* state, int64_t N, const int32_t* __restrict__ actions,
+                                              const int32_t* __restrict__ sel, float* __restrict__ out_reward,
+                                              uint8_t* __restrict__ out_terminal) {
+    int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
+    if (i >= N) return;
+    typename G::State s = G::load(state, N, i);
+    const int a = actions[i];
+    if (a >= 0) {
+        G::step(s, a, sel ? sel[i] : 0);
+        G::store(state, N, i, s);
+    }
+    if (out_reward) {
+        const float r = G::reward(s);
+        out_reward[2 * i] = r;
+        out_reward[2 * i + 1] = r;
+    }
+    if (out_terminal) out_terminal[i] = G::terminal(s) ? 1 : 0;
+}
+
+template <class G>
+__global__ void __launch_bounds__(BLK) k_legal_list(const uint32_t* state, int64_t N, int32_t* __restrict__ out_ids,
+                                                    int32_t* __restrict__ out_count) {
+    int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
+    if (i >= N) return;
+    typename G::State s = G::load(state, N, i);
+    int ids[G::LMAX];
+    int n = G::legal_list(s, ids);
+    for (int k = 0; k < G::LMAX; ++k) out_ids[i * G::LMAX + k] = k < n ? ids[k] : -1;
+    out_count[i] = n;
+}
+
+template <class G>
+__global__ void __launch_bounds__(BLK) k_outcome(const uint32_t* state, int64_t N, float* __restrict__ out) {
+    int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
+    if (i >= N) return;
+    typename G::State s = G::load(state, N, i);
+    float o0, o1;
+    G::outcome(s, o0, o1);
+    out[2 * i] = o0;
+    out[2 * i + 1] = o1;
+}
+
+template <class G>
+__global__ void __launch_bounds__(BLK) k_info(const uint32_t* state, int64_t N, int32_t* __restrict__ out) {
+    int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
+    if (i >= N) return;
+    typename G::State s = G::load(state, N, i);
+    float o0, o1;
+    G::outcome(s, o0, o1);
+    out[4 * i + 0] = G::turn(s);
+    out[4 * i + 1] = G::terminal(s) ? 1 : 0;
+    out[4 * i + 2] = G::steps(s);
+    out[4 * i + 3] = G::terminal(s) ? (o0 > 0 ? 1 : (o1 > 0 ? 2 : 3)) : 0;
+}
+
+// Stage this lane's bits, then let the warp stream the tile out.
+template <class G>
+__device__ __forceinline__ void emit_views(WarpStage<G>& st, const typename G::State& s, bool valid, int view,
+                                           int64_t g0, int ng, int lane, float* out_main, float* out_scalar,
+                                           float* out_amask, uint32_t* out_bits) {
+    uint32_t ob[G::OW], sc = 0, lm[G::LW];
+#pragma unroll
+    for (int k = 0; k < G::OW; ++k) ob[k] = 0;
+#pragma unroll
+    for (int k = 0; k < G::LW; ++k) lm[k] = 0;
+    if (valid) {
+        if (out_main || out_scalar) G::obs_bits(s, view, ob, sc);
+        if (out_amask || out_bits) G::legal_bits(s, lm);
+    }
+#pragma unroll
+    for (int k = 0; k < G::OW; ++k) st.obs[lane * G::OW + k] = ob[k];
+#pragma unroll
+    for (int k = 0; k < G::LW; ++k) st.legal[lane * G::LW + k] = lm[k];
+    st.scalar[lane] = sc;
+    if (out_bits && valid) {
+#pragma unroll
+        for (int k = 0; k < G::LW; ++k) out_bits[(g0 + lane) * G::LW + k] = lm[k];
+    }
+    __syncwarp();
+    if (out_main) emit_tile_f32<G::OBITS, G::OW>(st.obs, out_main + g0 * G::OBITS, ng, lane, 0.f, 1.f);
+    if (G::SBITS > 0 && out_scalar)
+        emit_tile_f32<(G::SBITS > 0 ? G::SBITS : 1), 1>(st.scalar, out_scalar + g0 * G::SBITS, ng, lane, 0.f, 1.f);
+    // action_mask = 1e32 on illegal, 0 on legal (generation.py:50-51)
+    if (out_amask) emit_tile_f32<G::A, G::LW>(st.legal, out_amask + g0 * G::A, ng, lane, 1e32f, 0.f);
+    __syncwarp();
+}
+
+template <class G>
+__global__ void __launch_bounds__(BLK) k_observe(const uint32_t* state, int64_t N, int view, const int32_t* views,
+                                                 float* out_main, float* out_scalar, float* out_amask,
+                                                 uint32_t* out_bits) {
+    __shared__ WarpStage<G> stage[WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t g0 = (blockIdx.x * (int64_t)WARPS + warp) * 32;
+    if (g0 >= N) return;
+    const int ng = (int)min((int64_t)32, N - g0);
+    const bool valid = lane < ng;
+    typename G::State s;
+    G::reset(s);
+    if (valid) s = G::load(state, N, g0 + lane);
+    const int v = (views && valid) ? views[g0 + lane] : view;
+    emit_views<G>(stage[warp], s, valid, v, g0, ng, lane, out_main, out_scalar, out_amask, out_bits);
+}
+
+// Fused ply: apply the chosen actions, report reward / terminal / outcome, optionally
+// restart finished games, then encode the next observation (turn player's view) and
+// legal mask — the body of generation.py:31-68 for N games in one launch.
+template <class G>
+__global__ void __launch_bounds__(BLK)
+k_step_observe(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, const int32_t* __restrict__ sel,
+               int auto_reset, float* out_main, float* out_scalar, float* out_amask, float* __restrict__ out_reward,
+               uint8_t* __restrict__ out_terminal, float* __restrict__ out_outcome, int32_t* __restrict__ out_turn) {
+    __shared__ WarpStage<G> stage[WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t g0 = (blockIdx.x * (int64_t)WARPS + warp) * 32;
+    if (g0 >= N) return;
+    const int ng = (int)min((int64_t)32, N - g0);
+    const bool valid = lane < ng;
+    const int64_t i = g0 + lane;
+    typename G::State s;
+    G::reset(s);
+    if (valid) {
+        s = G::load(state, N, i);
+        const int a = actions ? actions[i] : -1;
+        if (a >= 0) G::step(s, a, sel ? sel[i] : 0);
+        const bool term = G::terminal(s);
+        if (out_reward) {
+            const float r = G::reward(s);
+            out_reward[2 * i] = r;
+            out_reward[2 * i + 1] = r;
+        }
+        if (out_terminal) out_terminal[i] = term ? 1 : 0;
+        if (out_outcome) {
+            float o0, o1;
+            G::outcome(s, o0, o1);
+            out_outcome[2 * i] = o0;
+            out_outcome[2 * i + 1] = o1;
+        }
+        if (term && auto_reset) G::reset(s);
+        if (a >= 0 || (term && auto_reset)) G::store(state, N, i, s);
+        if (out_turn) out_turn[i] = G::turn(s);
+    }
+    emit_views<G>(stage[warp], s, valid, B200RL_VIEW_TURN, g0, ng, lane, out_main, out_scalar, out_amask, nullptr);
+}
+
+// k-th (0-based) set bit of an LW-word mask
+template <int LW>
+__device__ __forceinline__ int kth_set_bit(const uint32_t (&m)[LW], int k) {
+    int base = 0;
+#pragma unroll
+    for (int w = 0; w < LW; ++w) {
+        const int c = __popc(m[w]);
+        if (k < c) {
+            uint32_t x = m[w];
+            for (int j = 0; j < k; ++j) x &= x - 1;
+            return base + __ffs(x) - 1;
+        }
+        k -= c;
+        base += 32;
+    }
+    return -1;
+}
+
+struct RolloutParams {
+    uint32_t* state;
+    int64_t N;
+    int64_t n_plies;
+    uint64_t seed, game_id_base, it0;
+    float* out_main;    // [waves][N][OBITS] or null
+    float* out_scalar;  // [waves][N][SBITS] or null
+    float* out_amask;   // [waves][N][A] or null
+    int32_t* out_action;  // [waves][N] or null
+    int64_t waves;
+    uint4* traj;        // [D][2][N] compact records or null
+    int64_t D;
+    int32_t* ep_table;  // [E][4] = slot, steps | win << 16, end_it lo, end_it hi
+    int64_t E;
+    unsigned long long* counters;  // [0] episodes, [1] env steps, [2] BLACK wins, [3] WHITE wins, [4] draws
+};
+
+// Persistent self-play with the epoch-0 policy (uniform over legal actions ==
+// RandomModel's zero logits, handyrl/model.py:58-64): state stays in registers for
+// n_plies plies; every ply emits the reference-format moment data (observation,
+// action_mask, action) and/or a 32-byte compact trajectory record.
+template <class G>
+__global__ void __launch_bounds__(BLK) k_rollout(const RolloutParams p) {
+    __shared__ WarpStage<G> stage[WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t g0 = (blockIdx.x * (int64_t)WARPS + warp) * 32;
+    if (g0 >= p.N) return;
+    const int ng = (int)min((int64_t)32, p.N - g0);
+    const bool valid = lane < ng;
+    const int64_t i = g0 + lane;
+    typename G::State s;
+    G::reset(s);
+    if (valid) s = G::load(p.state, p.N, i);
+    unsigned int n_ep = 0, n_w0 = 0, n_w1 = 0, n_dr = 0;
+    const uint64_t stream_id = p.game_id_base + (uint64_t)i;
+
+    for (int64_t k = 0; k < p.n_plies; ++k) {
+        const uint64_t it = p.it0 + (uint64_t)k;
+        bool first = false;
+        if (valid && G::terminal(s)) G::reset(s);  // auto-reset: a finished slot starts its next episode
+        if (valid) first = G::steps(s) == 0;
+        // policy: uniform over the legal actions
+        uint32_t lm[G::LW];
+#pragma unroll
+        for (int w = 0; w < G::LW; ++w) lm[w] = 0;
+        int action = -1, selp = 0;
+        if (valid) {
+            G::legal_bits(s, lm);
+            int cnt = 0;
+#pragma unroll
+            for (int w = 0; w < G::LW; ++w) cnt += __popc(lm[w]);
+            const uint32_t r = b200rl_rand32(p.seed, stream_id, it);
+            const int kk = (int)__umulhi(r, (uint32_t)cnt);
+            action = kth_set_bit<G::LW>(lm, kk);
+            selp = (int)((r >> 7) & 1);  // ParallelTicTacToe: which player's move lands
+        }
+        const int64_t wv = p.waves > 0 ? (int64_t)(it % (uint64_t)p.waves) : 0;
+        if (p.out_main || p.out_amask || p.out_scalar) {
+            emit_views<G>(stage[warp], s, valid, B200RL_VIEW_TURN, g0, ng, lane,
+                          p.out_main ? p.out_main + wv * p.N * G::OBITS : nullptr,
+                          p.out_scalar ? p.out_scalar + wv * p.N * G::SBITS : nullptr,
+                          p.out_amask ? p.out_amask + wv * p.N * G::A : nullptr, nullptr);
+        }
+        if (valid) {
+            if (p.out_action) p.out_action[wv * p.N + i] = action;
+            uint32_t rec[8];
+            if (p.traj) G::pack_record(s, rec);
+            G::step(s, action, selp);
+            const bool term = G::terminal(s);
+            float o0 = 0.f, o1 = 0.f;
+            if (term) G::outcome(s, o0, o1);
+            const uint32_t wincode = term ? (o0 > 0 ? 1u : (o1 > 0 ? 2u : 3u)) : 0u;
+            if (p.traj) {
+                rec[5] = ((uint32_t)action & 0xFFFF) | ((uint32_t)selp << 16) | ((first ? 1u : 0u) << 24) |
+                         ((term ? 1u : 0u) << 25) | (wincode << 26);
+                rec[6] = (uint32_t)G::steps(s);
+                rec[7] = 0;
+                uint4* base = p.traj + (int64_t)(it % (uint64_t)p.D) * 2 * p.N;
+                base[i] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
+                base[p.N + i] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
+            }
+            if (term) {
+                n_ep += 1;
+                n_w0 += wincode == 1;
+                n_w1 += wincode == 2;
+                n_dr += wincode == 3;
+                if (p.ep_table) {
+                    unsigned long long idx = atomicAdd(&p.counters[5], 1ull);
+                    int32_t* e = p.ep_table + (int64_t)(idx % (unsigned long long)p.E) * 4;
+                    e[0] = (int32_t)i;
+                    e[1] = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
+                    e[2] = (int32_t)(uint32_t)it;
+                    e[3] = (int32_t)(uint32_t)(it >> 32);
+                }
+            }
+        }
+    }
+    if (valid) G::store(p.state, p.N, i, s);
+    if (p.counters) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            n_ep += __shfl_xor_sync(0xffffffffu, n_ep, o);
+            n_w0 += __shfl_xor_sync(0xffffffffu, n_w0, o);
+            n_w1 += __shfl_xor_sync(0xffffffffu, n_w1, o);
+            n_dr += __shfl_xor_sync(0xffffffffu, n_dr, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&p.counters[0], (unsigned long long)n_ep);
+            atomicAdd(&p.counters[1], (unsigned long long)ng * (unsigned long long)p.n_plies);
+            atomicAdd(&p.counters[2], (unsigned long long)n_w0);
+            atomicAdd(&p.counters[3], (unsigned long long)n_w1);
+            atomicAdd(&p.counters[4], (unsigned long long)n_dr);
+        }
+    }
+}
+
+inline int grid_for(int64_t N) { return (int)((N + BLK - 1) / BLK); }
+
+}  // namespace
+
+#define DISPATCH_GAME(game, EXPR)                                                       \
+    switch (game) {                                                                     \
+        case B200RL_GAME_TICTACTOE: { using G = TicTacToeGame<false>; EXPR; } break;     \
+        case B200RL_GAME_PARALLEL_TICTACTOE: { using G = TicTacToeGame<true>; EXPR; } break; \
+        case B200RL_GAME_GEISTER: { using G = GeisterGame<false>; EXPR; } break;         \
+        case B200RL_GAME_CIGEISTER: { using G = GeisterGame<true>; EXPR; } break;        \
+        default:                                                                        \
+            b200rl_set_error("unknown game id %d", game);                               \
+            return B200RL_ERR_ARG;                                                      \
+    }
+
+#define REQ_STATE(state, N)                                                                       \
+    B200RL_REQUIRE((state) != nullptr && (N) >= 0, "env: null state or negative N");             \
+    B200RL_REQUIRE(((uintptr_t)(state) % 16) == 0, "env: state must be 16-byte aligned");         \
+    if ((N) == 0) return B200RL_OK;
+
+extern "C" int64_t b200rl_env_state_bytes(int game) {
+    switch (game) {
+        case B200RL_GAME_TICTACTOE:
+        case B200RL_GAME_PARALLEL_TICTACTOE: return 4;
+        case B200RL_GAME_GEISTER:
+        case B200RL_GAME_CIGEISTER: return 64;
+    }
+    b200rl_set_error("unknown game id %d", game);
+    return -1;
+}
+
+extern "C" int b200rl_env_dims(int game, int64_t* out) {
+    B200RL_REQUIRE(out != nullptr, "env_dims: null out");
+    DISPATCH_GAME(game, {
+        out[0] = G::A; out[1] = G::OBITS; out[2] = G::SBITS; out[3] = G::LMAX; out[4] = G::LW;
+        out[5] = G::PLAYERS; out[6] = G::MAX_STEPS; out[7] = G::HAS_REWARD ? 1 : 0;
+    });
+    return B200RL_OK;
+}
+
+extern "C" int b200rl_env_reset(int game, void* state, int64_t N, const uint8_t* slot_mask, void* stream) {
+    REQ_STATE(state, N);
+    DISPATCH_GAME(game, (k_reset<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>((uint32_t*)state, N, slot_mask)));
+    return b200rl_check_launch("k_reset");
+}
+
+extern "C" int b200rl_env_step(int game, void* state, int64_t N, const int32_t* actions, const int32_t* selected,
+                               float* out_reward, uint8_t* out_terminal, void* stream) {
+    REQ_STATE(state, N);
+    B200RL_REQUIRE(actions != nullptr, "env_step: null actions");
+    DISPATCH_GAME(game, (k_step<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>((uint32_t*)state, N, actions,
+                                                                                  selected, out_reward, out_terminal)));
+    return b200rl_check_launch("k_step");
+}
+
+extern "C" int b200rl_env_legal_list(int game, const void* state, int64_t N, int32_t* out_ids, int32_t* out_count,
+                                     void* stream) {
+    REQ_STATE(state, N);
+    B200RL_REQUIRE(out_ids && out_count, "env_legal_list: null output");
+    DISPATCH_GAME(game, (k_legal_list<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>((const uint32_t*)state, N,
+                                                                                        out_ids, out_count)));
+    return b200rl_check_launch("k_legal_list");
+}
+
+extern "C" int b200rl_env_outcome(int game, const void* state, int64_t N, float* out, void* stream) {
+    REQ_STATE(state, N);
+    B200RL_REQUIRE(out != nullptr, "env_outcome: null output");
+    DISPATCH_GAME(game, (k_outcome<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>((const uint32_t*)state, N, out)));
+    return b200rl_check_launch("k_outcome");
+}
+
+extern "C" int b200rl_env_info(int game, const void* state, int64_t N, int32_t* out, void* stream) {
+    REQ_STATE(state, N);
+    B200RL_REQUIRE(out != nullptr, "env_info: null output");
+    DISPATCH_GAME(game, (k_info<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>((const uint32_t*)state, N, out)));
+    return b200rl_check_launch("k_info");
+}
+
+static bool aligned16(const void* p) { return ((uintptr_t)p % 16) == 0; }
+
+extern "C" int b200rl_env_observe(int game, const void* state, int64_t N, int view, const int32_t* views,
+                                  float* out_main, float* out_scalar, float* out_amask, uint32_t* out_bits,
+                                  void* stream) {
+    REQ_STATE(state, N);
+    B200RL_REQUIRE(view >= -1 && view <= 2, "env_observe: view must be -1 (None), 0, 1 or 2 (turn player)");
+    B200RL_REQUIRE(aligned16(out_main) && aligned16(out_scalar) && aligned16(out_amask),
+                   "env_observe: outputs must be 16-byte aligned");
+    DISPATCH_GAME(game, (k_observe<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(
+                            (const uint32_t*)state, N, view, views, out_main, out_scalar, out_amask, out_bits)));
+    return b200rl_check_launch("k_observe");
+}
+
+extern "C" int b200rl_env_step_observe(int game, void* state, int64_t N, const int32_t* actions,
+                                       const int32_t* selected, int auto_reset, float* out_main, float* out_scalar,
+                                       float* out_amask, float* out_reward, uint8_t* out_terminal,
+                                       float* out_outcome, int32_t* out_turn, void* stream) {
+    REQ_STATE(state, N);
+    B200RL_REQUIRE(aligned16(out_main) && aligned16(out_scalar) && aligned16(out_amask),
+                   "env_step_observe: outputs must be 16-byte aligned");
+    DISPATCH_GAME(game, (k_step_observe<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(
+                            (uint32_t*)state, N, actions, selected, auto_reset, out_main, out_scalar, out_amask,
+                            out_reward, out_terminal, out_outcome, out_turn)));
+    return b200rl_check_launch("k_step_observe");
+}
+
+extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_plies, uint64_t seed,
+                                  uint64_t game_id_base, uint64_t it0, float* out_main, float* out_scalar,
+                                  float* out_amask, int32_t* out_action, int64_t waves, void* traj, int64_t D,
+                                  int32_t* ep_table, int64_t E, uint64_t* counters, void* stream) {
+    REQ_STATE(state, N);
+    B200RL_REQUIRE(n_plies >= 0, "env_rollout: negative n_plies");
+    B200RL_REQUIRE(aligned16(out_main) && aligned16(out_scalar) && aligned16(out_amask) && aligned16(traj),
+                   "env_rollout: outputs must be 16-byte aligned");
+    B200RL_REQUIRE(!(out_main || out_scalar || out_amask || out_action) || waves >= 1, "env_rollout: waves must be >= 1");
+    B200RL_REQUIRE(!traj || D >= 1, "env_rollout: trajectory ring depth D must be >= 1");
+    B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_rollout: episode table needs E >= 1 and counters");
+    B200RL_REQUIRE(N % 4 == 0 || waves <= 1 || !(out_main || out_scalar || out_amask),
+                   "env_rollout: N must be a multiple of 4 when several waves are written");
+    RolloutParams p;
+    p.state = (uint32_t*)state; p.N = N; p.n_plies = n_plies; p.seed = seed; p.game_id_base = game_id_base;
+    p.it0 = it0; p.out_main = out_main; p.out_scalar = out_scalar; p.out_amask = out_amask;
+    p.out_action = out_action; p.waves = waves; p.traj = (uint4*)traj; p.D = D; p.ep_table = ep_table; p.E = E;
+    p.counters = (unsigned long long*)counters;
+    DISPATCH_GAME(game, (k_rollout<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(p)));
+    return b200rl_check_launch("k_rollout");
+}

@@ -71,6 +71,92 @@ int b200rl_target_mc(const float* values, int64_t v_sb, int64_t v_st, int64_t v_
                      const float* returns, int64_t ret_sb, int64_t ret_st, int64_t ret_sp,
                      float* out_adv, int64_t B, int64_t T, int64_t P, void* stream);
 
+/* ------------------------------------------------------------------ */
+/* Part 1: batched environments — handyrl/environment.py:43-146        */
+/* ------------------------------------------------------------------ */
+
+enum {
+    B200RL_GAME_TICTACTOE = 0,          /* handyrl/envs/tictactoe.py:72-172 */
+    B200RL_GAME_PARALLEL_TICTACTOE = 1, /* handyrl/envs/parallel_tictactoe.py:13-58 */
+    B200RL_GAME_GEISTER = 2,            /* handyrl/envs/geister.py:170-538 */
+    B200RL_GAME_CIGEISTER = 3           /* handyrl/envs/ci_geister.py (observation always shows opponent types) */
+};
+
+/* Observation view selector: observation(player) of the reference. */
+enum { B200RL_VIEW_NONE = -1, B200RL_VIEW_PLAYER0 = 0, B200RL_VIEW_PLAYER1 = 1, B200RL_VIEW_TURN = 2 };
+
+/*
+ * Game state lives in a caller-owned, 16-byte-aligned device buffer of
+ * N * b200rl_env_state_bytes(game) bytes (struct-of-arrays planes over the N
+ * games; opaque except through these calls and the layout documented in
+ * DESIGN.md).  Returns -1 for an unknown game.
+ */
+int64_t b200rl_env_state_bytes(int game);
+
+/* out[8] = action_length, observation floats (main tensor), scalar-observation floats,
+ * longest legal list, legal-mask words, players, max plies per episode, has_reward. */
+int b200rl_env_dims(int game, int64_t* out);
+
+/* Environment.reset() for all games, or for those with slot_mask[i] != 0. */
+int b200rl_env_reset(int game, void* state, int64_t N, const uint8_t* slot_mask, void* stream);
+
+/*
+ * Environment.step({player: action}) / play(action, player) for N games.
+ * actions[i] < 0 means "no action" (None).  `selected` (ParallelTicTacToe only,
+ * else NULL) is the player whose move lands (parallel_tictactoe.py:22).
+ * out_reward (N,2) = reward() after the ply, out_terminal (N) = terminal(); either may be NULL.
+ */
+int b200rl_env_step(int game, void* state, int64_t N, const int32_t* actions, const int32_t* selected,
+                    float* out_reward, uint8_t* out_terminal, void* stream);
+
+/* legal_actions() as an ordered list (reference order), ids (N, LMAX) padded with -1, count (N). */
+int b200rl_env_legal_list(int game, const void* state, int64_t N, int32_t* out_ids, int32_t* out_count,
+                          void* stream);
+
+/*
+ * observation(player) and the legal mask of the player to move.
+ *   view / views : one selector for all games, or per-game selectors (N) when views != NULL
+ *   out_main     : (N, 7,6,6) Geister 'board' / (N, 3,3,3) TicTacToe, fp32, or NULL
+ *   out_scalar   : (N, 18) Geister 'scalar', or NULL
+ *   out_amask    : (N, A) fp32, 0 on legal and 1e32 on illegal actions (generation.py:50-51), or NULL
+ *   out_bits     : (N, LW) uint32 bit mask of legal action ids, or NULL
+ */
+int b200rl_env_observe(int game, const void* state, int64_t N, int view, const int32_t* views, float* out_main,
+                       float* out_scalar, float* out_amask, uint32_t* out_bits, void* stream);
+
+/* outcome() -> (N, 2) fp32. */
+int b200rl_env_outcome(int game, const void* state, int64_t N, float* out, void* stream);
+
+/* (N, 4) int32: turn(), terminal(), plies played (incl. setup), winner code (0 none, 1 player0, 2 player1, 3 draw). */
+int b200rl_env_info(int game, const void* state, int64_t N, int32_t* out, void* stream);
+
+/*
+ * One fused ply of the self-play loop (generation.py:31-68) for N games: apply
+ * `actions` (NULL = observe only), write reward / terminal / outcome of the
+ * resulting state, restart finished games when auto_reset != 0, then write the
+ * turn player's observation and action mask of the state the next ply starts from.
+ */
+int b200rl_env_step_observe(int game, void* state, int64_t N, const int32_t* actions, const int32_t* selected,
+                            int auto_reset, float* out_main, float* out_scalar, float* out_amask,
+                            float* out_reward, uint8_t* out_terminal, float* out_outcome, int32_t* out_turn,
+                            void* stream);
+
+/*
+ * Persistent self-play with the epoch-0 policy (RandomModel: uniform over legal
+ * actions, handyrl/model.py:58-64; handyrl/train.py:438-439) for n_plies plies per
+ * game with auto-reset; every game performs exactly one env-step per ply.
+ *   seed, game_id_base, it0 : counter-RNG key (seed, game_id_base + slot, it0 + ply)
+ *   out_main/out_scalar/out_amask/out_action : moment data of ply `it`, written to wave
+ *       (it % waves) of [waves][N][...] buffers; any may be NULL
+ *   traj : [D][2][N] uint4 ring of 32-byte compact records, or NULL
+ *   ep_table : (E, 4) int32 ring of finished episodes {slot, steps | win << 16, end_it lo, hi}
+ *   counters : uint64[8] {episodes, env steps, player0 wins, player1 wins, draws, ep_table cursor, -, -}
+ */
+int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_plies, uint64_t seed, uint64_t game_id_base,
+                       uint64_t it0, float* out_main, float* out_scalar, float* out_amask, int32_t* out_action,
+                       int64_t waves, void* traj, int64_t D, int32_t* ep_table, int64_t E, uint64_t* counters,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,66 @@
+"""CPU: the C oracle of the game rules against tapes recorded from the reference itself."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import games_c
+
+ENVS = ['tictactoe', 'parallel_tictactoe', 'geister', 'ci_geister']
+
+
+def _bits(a, n):
+    return np.unpackbits(a, bitorder='little')[:n].astype(np.float32)
+
+
+@pytest.mark.parametrize("env", ENVS)
+def test_c_oracle_replays_reference_tapes(golden_dir, env):
+    t = np.load(os.path.join(golden_dir, "tape_%s.npz" % env))
+    geister = 'geister' in env
+    nmain = 252 if geister else 27
+    e = games_c.Env(env)
+    game = -1
+    n_states = len(t['game'])
+    for i in range(n_states):
+        if t['game'][i] != game:
+            game = t['game'][i]
+            e.reset()
+            assert t['action'][i] == -1
+        else:
+            e.step(t['action'][i], t['sel'][i])
+            assert abs(e.reward() - t['reward'][i]) < 1e-9 or not geister
+        assert e.terminal() == bool(t['terminal'][i])
+        if env != 'parallel_tictactoe':
+            assert e.turn() == t['turn'][i]
+        legal = list(t['legal_flat'][t['legal_off'][i]:t['legal_off'][i + 1]])
+        assert e.legal_actions() == legal, (i, e.legal_actions(), legal)
+        for key, pl in (('0', 0), ('1', 1), ('N', None)):
+            main, sc = e.observation(pl)
+            np.testing.assert_array_equal(main, _bits(t['obs' + key][i], nmain))
+            if geister:
+                np.testing.assert_array_equal(sc, _bits(t['sc' + key][i], 18))
+        last = i + 1 == n_states or t['game'][i + 1] != game
+        if last:
+            assert e.terminal()
+            assert e.outcome() == list(t['outcome'][game])
+
+
+@pytest.mark.parametrize("env", ENVS)
+def test_c_random_tapes_are_self_consistent(env):
+    d = games_c.random_tapes(env, 20, seed=3)
+    assert d['terminal'].sum() == 20
+    e = games_c.Env(env)
+    # replaying the recorded actions reproduces the recorded legal lists
+    game = -1
+    for i in range(len(d['game'])):
+        if d['game'][i] != game:
+            game = d['game'][i]
+            e.reset()
+        else:
+            e.step(d['action'][i], d['sel'][i])
+        n = d['legal_count'][i]
+        assert e.legal_actions() == list(d['legal_ids'][i][:n])
+
+
+def test_selfplay_baseline_driver_runs():
+    assert games_c.selfplay('geister', 2000, seed=1, n_threads=2) == 4000

@@ -1,0 +1,128 @@
+"""GPU: the persistent self-play kernel (uniform epoch-0 policy).  Its action tape is
+replayed through the C oracle: observations, action masks, terminal flags, winners,
+episode table and counters must match bit-exactly."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import games_c
+
+pytestmark = pytest.mark.gpu
+ENVS = {'tictactoe': 'TicTacToe', 'parallel_tictactoe': 'ParallelTicTacToe', 'geister': 'Geister',
+        'ci_geister': 'CIGeister'}
+
+
+def _rollout(env_key, N, K, chunks=1, seed=7):
+    from handyrl_b200.engine import BatchedEnv
+    env = BatchedEnv(ENVS[env_key], N)
+    main, scalar = env.alloc_obs(waves=K)
+    waves = dict(main=main, scalar=scalar, action_mask=torch.empty(K, N, env.A, device='cuda'))
+    act = torch.full((K, N), -9, dtype=torch.int32, device='cuda')
+    traj = torch.zeros(K, 2, N, 4, dtype=torch.int32, device='cuda')
+    ept = torch.zeros(4 * N * K // 2 + 16, 4, dtype=torch.int32, device='cuda')
+    ctr = torch.zeros(8, dtype=torch.int64, device='cuda')
+    per = K // chunks
+    for c in range(chunks):
+        env.rollout(per, seed=seed, waves=waves, traj=traj, ep_table=ept, counters=ctr, out_action=act)
+    torch.cuda.synchronize()
+    return env, waves, act.cpu().numpy(), traj.cpu().numpy(), ept.cpu().numpy(), ctr.cpu().numpy()
+
+
+@pytest.mark.parametrize("env_key,N,K", [('tictactoe', 96, 64), ('parallel_tictactoe', 96, 64), ('geister', 70, 420),
+                                         ('ci_geister', 33, 250)])
+def test_rollout_replays_through_oracle(env_key, N, K):
+    env, waves, act, traj, ept, ctr = _rollout(env_key, N, K)
+    geister = 'geister' in env_key
+    main = waves['main'].cpu().numpy().reshape(K, N, -1)
+    scalar = waves['scalar'].cpu().numpy() if geister else None
+    amask = waves['action_mask'].cpu().numpy()
+    flags = traj[:, 1, :, 1].view(np.uint32)
+    n_ep = 0
+    wins = [0, 0, 0, 0]
+    episodes = []
+    for g in range(N):
+        e = games_c.Env(env_key)
+        steps = 0
+        for k in range(K):
+            f = int(flags[k, g])
+            a, sel, first, term, win = f & 0xFFFF, (f >> 16) & 1, (f >> 24) & 1, (f >> 25) & 1, (f >> 26) & 3
+            assert a == act[k, g]
+            if e.terminal():
+                e.reset()
+                steps = 0
+            assert first == (steps == 0)
+            m, sc = e.observation(e.turn() if env_key != 'parallel_tictactoe' else 0)
+            np.testing.assert_array_equal(main[k, g], m)
+            if geister:
+                np.testing.assert_array_equal(scalar[k, g], sc)
+            legal = e.legal_actions()
+            ref_am = np.full(env.A, 1e32, dtype=np.float32)
+            ref_am[legal] = 0
+            np.testing.assert_array_equal(amask[k, g], ref_am)
+            assert a in legal
+            e.step(a, sel)
+            steps += 1
+            assert term == int(e.terminal())
+            assert int(traj[k, 1, g, 2]) == steps
+            if term:
+                oc = e.outcome()
+                code = 1 if oc[0] > 0 else (2 if oc[1] > 0 else 3)
+                assert win == code
+                wins[code] += 1
+                n_ep += 1
+                episodes.append((g, steps | (code << 16), k))
+    assert ctr[0] == n_ep and ctr[1] == N * K and ctr[5] == n_ep
+    assert list(ctr[2:5]) == wins[1:]
+    got = sorted((int(r[0]), int(r[1]), int(r[2])) for r in ept[:n_ep])
+    assert got == sorted(episodes)
+    # final device state == oracle state (via observation of every view)
+    ob = env.observe(view=-1)
+    assert ob['main'].shape[0] == N
+
+
+def test_rollout_is_chunk_invariant_and_seeded():
+    a = _rollout('geister', 64, 128, chunks=1, seed=3)
+    b = _rollout('geister', 64, 128, chunks=4, seed=3)
+    c = _rollout('geister', 64, 128, chunks=1, seed=4)
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
+    assert not np.array_equal(a[2], c[2])
+    assert torch.equal(a[0].state, b[0].state)
+
+
+def test_uniform_policy_statistics():
+    """First TicTacToe move is uniform over 9 cells; Geister setup over 70 layouts."""
+    from handyrl_b200.engine import BatchedEnv
+    N = 90000
+    for game, A, lo in (('TicTacToe', 9, 0), ('Geister', 70, 144)):
+        env = BatchedEnv(game, N)
+        act = torch.zeros(1, N, dtype=torch.int32, device='cuda')
+        env.rollout(1, seed=5, out_action=act)
+        h = torch.bincount(act[0].long() - lo, minlength=A).cpu().numpy()
+        assert h.sum() == N and len(h) == A
+        exp = N / A
+        chi2 = ((h - exp) ** 2 / exp).sum()
+        assert chi2 < 3 * A, (chi2, h)
+
+
+def test_full_size_rollout_invariants():
+    """BASELINE size: 65,536 concurrent Geister games; invariants that need no oracle."""
+    from handyrl_b200.engine import BatchedEnv
+    N, K = 65536, 256
+    env = BatchedEnv('Geister', N)
+    ctr = torch.zeros(8, dtype=torch.int64, device='cuda')
+    main, scalar = env.alloc_obs(waves=1)
+    waves = dict(main=main, scalar=scalar, action_mask=torch.empty(1, N, env.A, device='cuda'))
+    env.rollout(K, seed=1, waves=waves, counters=ctr)
+    c = ctr.cpu().numpy()
+    assert c[1] == N * K
+    assert c[0] == c[2] + c[3] + c[4] and c[0] > N // 2   # every finished game has exactly one result
+    info = env.info().cpu().numpy()
+    assert info[:, 2].max() <= 202 and info[:, 2].min() >= 1
+    m = waves['main'][0]
+    assert bool((m[:, 0] == 1).all())                        # plane 0 is all ones
+    assert bool(((m == 0) | (m == 1)).all())
+    assert bool((m[:, 1] + m[:, 2] <= 1).all())              # a cell is not both mine and theirs
+    assert bool((m[:, 3] + m[:, 4] == m[:, 1]).all())        # my blue + my red == my pieces
+    assert bool((m[:, 5:7] == 0).all())                      # hidden opponent types (Geister, player view)
+    am = waves['action_mask'][0]
+    assert bool(((am == 0) | (am == 1e32)).all()) and bool(((am == 0).sum(1) >= 1).all())

@@ -39,6 +39,81 @@ def gen_targets():
     print("targets.npz:", len(out), "arrays")
 
 
+def _obs_to_bits(o):
+    """reference observation -> (main bits packed uint8, scalar bits packed uint8)"""
+    if isinstance(o, dict):
+        main, scalar = np.ascontiguousarray(o['board']).reshape(-1), np.asarray(o['scalar']).reshape(-1)
+    else:
+        main, scalar = np.asarray(o).reshape(-1), np.zeros(0, np.float32)
+    for a in (main, scalar):
+        assert a.dtype == np.float32 and np.all((a == 0) | (a == 1))
+    return (np.packbits(main.astype(np.uint8), bitorder='little'),
+            np.packbits(scalar.astype(np.uint8), bitorder='little'))
+
+
+def _play_tapes(env_module, n_games, parallel, seed0):
+    """Random self-play through the REFERENCE env; records every state and action."""
+    import random
+    rec = dict(game=[], action=[], sel=[], turn=[], terminal=[], reward=[], legal_flat=[], legal_off=[0],
+               obs0=[], obs1=[], obsN=[], sc0=[], sc1=[], scN=[], outcome=[], steps=[])
+    for g in range(n_games):
+        random.seed(seed0 + g)
+        e = env_module.Environment()
+        e.reset()
+
+        def snap(action, sel, reward):
+            rec['game'].append(g)
+            rec['action'].append(action)
+            rec['sel'].append(sel)
+            t = e.turn()
+            rec['turn'].append(t if isinstance(t, int) or hasattr(t, '__index__') else 0)
+            rec['terminal'].append(1 if e.terminal() else 0)
+            rec['reward'].append(reward)
+            la = [int(a) for a in e.legal_actions(0)]
+            rec['legal_flat'] += la
+            rec['legal_off'].append(len(rec['legal_flat']))
+            for key, pl in (('0', 0), ('1', 1), ('N', None)):
+                m, sc = _obs_to_bits(e.observation(pl))
+                rec['obs' + key].append(m)
+                rec['sc' + key].append(sc)
+
+        snap(-1, 0, 0.0)
+        steps = 0
+        while not e.terminal():
+            actions = {p: random.choice(e.legal_actions(p)) for p in e.turns()}
+            e.step(actions)
+            steps += 1
+            if parallel:
+                color, act = e.record[-1]
+                sel = 0 if color == e.BLACK else 1
+            else:
+                act, sel = list(actions.values())[0], 0
+            r = e.reward()
+            snap(int(act), sel, float(r.get(0, 0.0)) if r else 0.0)
+        oc = e.outcome()
+        rec['outcome'].append([oc[0], oc[1]])
+        rec['steps'].append(steps)
+    out = {}
+    for k, v in rec.items():
+        if k.startswith('obs') or k.startswith('sc'):
+            out[k] = np.stack(v).astype(np.uint8)
+        elif k in ('reward', 'outcome'):
+            out[k] = np.asarray(v, dtype=np.float32)
+        else:
+            out[k] = np.asarray(v, dtype=np.int32)
+    return out
+
+
+def gen_games():
+    import importlib
+    for name, n_games, parallel in (('tictactoe', 200, False), ('parallel_tictactoe', 200, True),
+                                    ('geister', 48, False), ('ci_geister', 16, False)):
+        mod = importlib.import_module('handyrl.envs.' + name)
+        out = _play_tapes(mod, n_games, parallel, seed0=1000)
+        np.savez_compressed(os.path.join(GOLD, "tape_%s.npz" % name), **out)
+        print("tape_%s.npz: %d games, %d states" % (name, n_games, len(out['game'])))
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     os.makedirs(GOLD, exist_ok=True)
