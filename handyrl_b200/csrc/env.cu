@@ -427,8 +427,8 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     B200RL_REQUIRE(!(out_main || out_scalar || out_amask || out_action) || waves >= 1, "env_rollout: waves must be >= 1");
     B200RL_REQUIRE(!traj || D >= 1, "env_rollout: trajectory ring depth D must be >= 1");
     B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_rollout: episode table needs E >= 1 and counters");
-    B200RL_REQUIRE(N % 4 == 0 || waves <= 1 || !(out_main || out_scalar || out_amask),
-                   "env_rollout: N must be a multiple of 4 when several waves are written");
+    B200RL_REQUIRE(N % 2 == 0 || waves <= 1 || !(out_main || out_scalar || out_amask),
+                   "env_rollout: N must be even when several waves are written (16-byte aligned wave bases)");
     RolloutParams p;
     p.state = (uint32_t*)state; p.N = N; p.n_plies = n_plies; p.seed = seed; p.game_id_base = game_id_base;
     p.it0 = it0; p.out_main = out_main; p.out_scalar = out_scalar; p.out_amask = out_amask;

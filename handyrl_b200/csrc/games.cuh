@@ -18,14 +18,7 @@
 #pragma once
 #include "common.cuh"
 
-#define B200RL_GAME_TICTACTOE 0
-#define B200RL_GAME_PARALLEL_TICTACTOE 1
-#define B200RL_GAME_GEISTER 2
-#define B200RL_GAME_CIGEISTER 3
-
-// View selector for observations.
-#define B200RL_VIEW_NONE (-1)  // observation(player=None)
-#define B200RL_VIEW_TURN 2     // observation(turn player)
+#include "../../include/b200rl.h"  // game ids and view selectors
 
 // ---------------------------------------------------------------------------
 // TicTacToe / ParallelTicTacToe

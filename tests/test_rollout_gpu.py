@@ -29,7 +29,7 @@ def _rollout(env_key, N, K, chunks=1, seed=7):
 
 
 @pytest.mark.parametrize("env_key,N,K", [('tictactoe', 96, 64), ('parallel_tictactoe', 96, 64), ('geister', 70, 420),
-                                         ('ci_geister', 33, 250)])
+                                         ('ci_geister', 34, 250)])
 def test_rollout_replays_through_oracle(env_key, N, K):
     env, waves, act, traj, ept, ctr = _rollout(env_key, N, K)
     geister = 'geister' in env_key
