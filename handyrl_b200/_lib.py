@@ -54,6 +54,11 @@ SIGNATURES = {
     "b200rl_env_step_observe": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_int] + [c_ptr] * 8,
     "b200rl_env_rollout": [c_int, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
                            c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr],
+    "b200rl_env_step_record": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_int, c_ptr, c_i64, c_u64, c_ptr, c_i64,
+                               c_ptr, c_ptr, c_ptr],
+    "b200rl_make_batch": [c_int, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_int, c_ptr,
+                          c_i64] + [c_ptr] * 14,
+    "b200rl_pad_stack": [c_ptr, c_ptr, c_ptr, ctypes.c_uint32, c_ptr, c_i64, c_i64, c_i64, c_ptr],
 }
 
 # functions that return a value instead of a status

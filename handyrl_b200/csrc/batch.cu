@@ -1,0 +1,339 @@
+// Episode-to-batch assembly (handyrl/train.py:33-133 make_batch) from the device
+// trajectory ring, plus the recording step that fills the ring.
+//
+// The ring holds one 32-byte record per (ply, game slot): the compact pre-move
+// state, the action(s) and episode flags.  make_batch re-encodes observation,
+// policy and action_mask from the record instead of copying 2.8 kB of fp32 per
+// (b, t): HBM reads are 32 B per cell, writes are the batch tensors themselves.
+#include "common.cuh"
+#include "games.cuh"
+#include "emit.cuh"
+#include "../../include/b200rl.h"
+
+namespace {
+
+constexpr int BLK = 128;
+constexpr int WARPS = BLK / 32;
+
+// ---------------------------------------------------------------------------
+// step + record: one ply driven by caller-chosen actions (net-in-the-loop self-play
+// or tape replay), writing the same trajectory records as k_rollout.
+// ---------------------------------------------------------------------------
+template <class G>
+__global__ void __launch_bounds__(BLK)
+k_step_record(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, const int32_t* __restrict__ sel,
+              const int32_t* __restrict__ both, int auto_reset, uint4* traj, int64_t D, uint64_t it,
+              int32_t* ep_table, int64_t E, unsigned long long* counters, uint8_t* __restrict__ out_terminal) {
+    const int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
+    if (i >= N) return;
+    typename G::State s = G::load(state, N, i);
+    if (auto_reset && G::terminal(s)) G::reset(s);
+    const int a = actions[i];
+    if (a < 0) {  // no ply for this slot
+        if (out_terminal) out_terminal[i] = G::terminal(s) ? 1 : 0;
+        G::store(state, N, i, s);
+        return;
+    }
+    const bool first = G::steps(s) == 0;
+    const int selp = sel ? sel[i] : 0;
+    uint32_t rec[8];
+    G::pack_record(s, rec);
+    G::step(s, a, selp);
+    const bool term = G::terminal(s);
+    float o0 = 0.f, o1 = 0.f;
+    if (term) G::outcome(s, o0, o1);
+    const uint32_t wincode = term ? (o0 > 0 ? 1u : (o1 > 0 ? 2u : 3u)) : 0u;
+    rec[5] = ((uint32_t)a & 0xFFFF) | ((uint32_t)(selp & 1) << 16) | ((first ? 1u : 0u) << 24) |
+             ((term ? 1u : 0u) << 25) | (wincode << 26);
+    rec[6] = (uint32_t)G::steps(s);
+    rec[7] = both ? (((uint32_t)both[2 * i] & 0xFF) | (((uint32_t)both[2 * i + 1] & 0xFF) << 8)) : 0u;
+    uint4* base = traj + (int64_t)(it % (uint64_t)D) * 2 * N;
+    base[i] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
+    base[N + i] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
+    if (term && counters) {
+        atomicAdd(&counters[0], 1ull);
+        atomicAdd(&counters[1 + wincode], 1ull);
+        if (ep_table) {
+            unsigned long long idx = atomicAdd(&counters[5], 1ull);
+            int32_t* e = ep_table + (int64_t)(idx % (unsigned long long)E) * 4;
+            e[0] = (int32_t)i;
+            e[1] = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
+            e[2] = (int32_t)(uint32_t)it;
+            e[3] = (int32_t)(uint32_t)(it >> 32);
+        }
+    }
+    if (out_terminal) out_terminal[i] = term ? 1 : 0;
+    G::store(state, N, i, s);
+}
+
+// ---------------------------------------------------------------------------
+// make_batch
+// ---------------------------------------------------------------------------
+enum { MB_TURN = 0, MB_ALL = 1, MB_SOLO = 2 };
+
+struct BatchParams {
+    const uint4* traj;
+    int64_t D, N;
+    const float* values;  // [D][N][2] value estimates recorded with the ring, or null (RandomModel: 0)
+    const float* logits;  // [D][N][A] behaviour logits, or null (RandomModel: zero logits)
+    const int32_t* win;   // [B][8] = slot, it_lo, it_hi, len, st, total, wincode, solo player
+    const float* ret_table;  // discounted return of a ply with m plies left, m = 0..ret_len-1
+    int ret_len;
+    int64_t B;
+    int T, mode, obs_all;
+    float *obs_main, *obs_scalar, *policy, *amask;
+    long long* action;
+    float *value, *reward, *ret, *outcome, *emask, *tmask, *omask, *progress;
+};
+
+// per-warp staging for 32 cells x up to 2 observed players
+template <class G>
+struct BatchStage {
+    uint32_t obs[64 * G::OW];
+    uint32_t legal[64 * G::LW];   // 1 = legal                (action_mask: 0 / 1e32)
+    uint32_t illegal[64 * G::LW]; // 1 = illegal on a live row (policy: -1e32 / 0)
+    uint32_t scalar[64];
+};
+
+template <class G>
+__global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
+    __shared__ BatchStage<G> stage[WARPS];
+    BatchStage<G>& st = stage[threadIdx.x >> 5];
+    const int lane = threadIdx.x & 31;
+    const int64_t ncell = p.B * p.T;
+    const int64_t c0 = (blockIdx.x * (int64_t)WARPS + (threadIdx.x >> 5)) * 32;
+    if (c0 >= ncell) return;
+    const int nc = (int)min((int64_t)32, ncell - c0);
+    const bool valid = lane < nc;
+    const int64_t c = c0 + lane;
+    const int Po = p.mode == MB_ALL ? 2 : 1;   // players carrying observation / policy
+    const int Pv = p.mode == MB_SOLO ? 1 : 2;  // players carrying value / reward / return
+
+    // ---- per-cell integer work ----
+    uint32_t ob[2][G::OW], sc[2] = {0, 0}, lg[2][G::LW], il[2][G::LW];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+#pragma unroll
+        for (int k = 0; k < G::OW; ++k) ob[q][k] = 0;
+#pragma unroll
+        for (int k = 0; k < G::LW; ++k) lg[q][k] = il[q][k] = 0;
+    }
+    if (valid) {
+        const int64_t b = c / p.T;
+        const int t = (int)(c - b * p.T);
+        const int32_t* w = p.win + b * 8;
+        const int len = w[3], stt = w[4], total = w[5], wincode = w[6], solo = w[7];
+        const float oc0 = wincode == 1 ? 1.f : (wincode == 2 ? -1.f : 0.f);
+        const float oc1 = wincode == 1 ? -1.f : (wincode == 2 ? 1.f : 0.f);
+        const bool live = t < len;
+        long long act[2] = {0, 0};
+        float val[2] = {oc0, oc1}, rew[2] = {0.f, 0.f}, rtn[2] = {0.f, 0.f}, tm[2] = {0.f, 0.f}, om[2] = {0.f, 0.f};
+        if (live) {
+            const uint64_t it = ((uint64_t)(uint32_t)w[1] | ((uint64_t)(uint32_t)w[2] << 32)) + (uint64_t)t;
+            const int64_t slot = w[0];
+            const uint4* base = p.traj + (int64_t)(it % (uint64_t)p.D) * 2 * p.N;
+            const uint4 r0 = base[slot], r1 = base[p.N + slot];
+            uint32_t rec[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+            typename G::State s = G::unpack_record(rec);
+            const int tp = G::turn(s);  // m['turn'][0]
+            const bool parallel = G::SIMULTANEOUS;
+            const int a_turn = (int)(rec[5] & 0xFFFF);
+            int pa[2] = {a_turn, a_turn};
+            if (parallel) { pa[0] = (int)(rec[7] & 0xFF); pa[1] = (int)((rec[7] >> 8) & 0xFF); }
+            uint32_t lm[G::LW];
+            G::legal_bits(s, lm);
+            for (int q = 0; q < Po; ++q) {
+                // which player does output slot q describe?
+                const int pl = p.mode == MB_TURN ? tp : (p.mode == MB_SOLO ? solo : q);
+                const bool is_turn = parallel || pl == tp;
+                // observation exists for turn players, and for everyone when args['observation'];
+                // otherwise it is the zero template (train.py:60,70)
+                const bool has_obs = is_turn || p.obs_all;
+                if (has_obs) G::obs_bits(s, pl, ob[q], sc[q]);
+                if (is_turn) {
+#pragma unroll
+                    for (int k = 0; k < G::LW; ++k) {
+                        lg[q][k] = lm[k];
+                        il[q][k] = ~lm[k];
+                    }
+                    il[q][G::LW - 1] &= (G::A % 32) ? ((1u << (G::A % 32)) - 1u) : 0xFFFFFFFFu;
+                    act[q] = parallel ? pa[pl] : a_turn;
+                }
+            }
+            for (int q = 0; q < Pv; ++q) {
+                const int pl = p.mode == MB_SOLO ? solo : q;
+                const bool is_turn = parallel || pl == tp;
+                const bool observed = is_turn || p.obs_all;
+                float v = 0.f;
+                if (observed && p.values) v = p.values[((int64_t)(it % (uint64_t)p.D) * p.N + slot) * 2 + pl];
+                val[q] = v;
+                rew[q] = G::HAS_REWARD ? G::reward(s) : 0.f;
+                const int left = total - (stt + t);
+                rtn[q] = (G::HAS_REWARD && left >= 0 && left < p.ret_len) ? p.ret_table[left] : 0.f;
+                tm[q] = is_turn ? 1.f : 0.f;
+                om[q] = observed ? 1.f : 0.f;
+            }
+        } else if (p.mode == MB_SOLO) {
+            val[0] = solo == 0 ? oc0 : oc1;
+        }
+        // ---- small per-cell tensors ----
+        for (int q = 0; q < Po; ++q) p.action[c * Po + q] = act[q];
+        for (int q = 0; q < Pv; ++q) {
+            p.value[c * Pv + q] = val[q];
+            p.reward[c * Pv + q] = rew[q];
+            p.ret[c * Pv + q] = rtn[q];
+            p.tmask[c * Pv + q] = tm[q];
+            p.omask[c * Pv + q] = om[q];
+        }
+        p.emask[c] = live ? 1.f : 0.f;
+        p.progress[c] = live ? __fdiv_rn((float)(stt + t), (float)total) : 1.f;
+        if (t == 0) {
+            if (p.mode == MB_SOLO) p.outcome[b] = solo == 0 ? oc0 : oc1;
+            else { p.outcome[b * 2] = oc0; p.outcome[b * 2 + 1] = oc1; }
+        }
+    }
+    // ---- stage bits, then stream the big tensors ----
+    for (int q = 0; q < Po; ++q) {
+        const int si = lane * Po + q;
+#pragma unroll
+        for (int k = 0; k < G::OW; ++k) st.obs[si * G::OW + k] = ob[q][k];
+#pragma unroll
+        for (int k = 0; k < G::LW; ++k) {
+            st.legal[si * G::LW + k] = lg[q][k];
+            st.illegal[si * G::LW + k] = il[q][k];
+        }
+        st.scalar[si] = sc[q];
+    }
+    __syncwarp();
+    const int ng = nc * Po;
+    emit_tile_f32<G::OBITS, G::OW>(st.obs, p.obs_main + c0 * Po * G::OBITS, ng, lane, 0.f, 1.f);
+    if (G::SBITS > 0)
+        emit_tile_f32<(G::SBITS > 0 ? G::SBITS : 1), 1>(st.scalar, p.obs_scalar + c0 * Po * G::SBITS, ng, lane, 0.f,
+                                                        1.f);
+    emit_tile_f32<G::A, G::LW>(st.legal, p.amask + c0 * Po * G::A, ng, lane, 1e32f, 0.f);
+    if (p.logits == nullptr) {
+        // RandomModel: policy = 0 - action_mask on live turn rows, 0 elsewhere (train.py:61,70,94)
+        emit_tile_f32<G::A, G::LW>(st.illegal, p.policy + c0 * Po * G::A, ng, lane, 0.f, -1e32f);
+    }
+}
+
+// policy = logits - action_mask for recorded behaviour logits (generation.py:52): one warp per
+// (cell, player) row; rows without any legal action (padding, non-turn players) stay zero.
+template <class G>
+__global__ void __launch_bounds__(BLK) k_policy_from_logits(const BatchParams p) {
+    const int Po = p.mode == MB_ALL ? 2 : 1;
+    const int lane = threadIdx.x & 31;
+    const int64_t rows = p.B * p.T * Po;
+    const int64_t r = blockIdx.x * (int64_t)WARPS + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int64_t c = r / Po;
+    const int64_t b = c / p.T;
+    const int t = (int)(c - b * p.T);
+    const int32_t* w = p.win + b * 8;
+    bool any = false;
+    for (int a = lane; a < G::A; a += 32) any |= p.amask[r * G::A + a] == 0.f;
+    any = __any_sync(0xffffffffu, any);
+    const bool live = t < w[3] && any;
+    const uint64_t it = ((uint64_t)(uint32_t)w[1] | ((uint64_t)(uint32_t)w[2] << 32)) + (uint64_t)t;
+    const float* lg = p.logits + ((int64_t)(it % (uint64_t)p.D) * p.N + w[0]) * G::A;
+    for (int a = lane; a < G::A; a += 32)
+        p.policy[r * G::A + a] = live ? __fsub_rn(lg[a], p.amask[r * G::A + a]) : 0.f;
+}
+
+// Ragged -> padded stack for host-decoded reference episodes: out[b][t][:] = src[off[b]+t][:]
+// for t < off[b+1]-off[b], else fill_rows[b][:] (value <- outcome, train.py:96) or the constant.
+__global__ void __launch_bounds__(256)
+k_pad_stack(const uint32_t* __restrict__ src, const int64_t* __restrict__ off, const uint32_t* __restrict__ fill_rows,
+            uint32_t fill, uint32_t* __restrict__ out, int64_t B, int64_t T, int64_t row) {
+    const int64_t n = B * T * row;
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t j = e % row;
+        const int64_t bt = e / row;
+        const int64_t t = bt % T, b = bt / T;
+        const int64_t len = off[b + 1] - off[b];
+        uint32_t v;
+        if (t < len) v = src[(off[b] + t) * row + j];
+        else v = fill_rows ? fill_rows[b * row + j] : fill;
+        out[e] = v;
+    }
+}
+
+inline int grid_for(int64_t n) { return (int)((n + BLK - 1) / BLK); }
+
+template <class G>
+int launch_make_batch(const BatchParams& p, cudaStream_t stream) {
+    B200RL_REQUIRE(G::SBITS == 0 || p.obs_scalar, "make_batch: this game needs obs_scalar");
+    const int64_t ncell = p.B * p.T;
+    const int Po = p.mode == MB_ALL ? 2 : 1;
+    k_make_batch<G><<<grid_for(ncell), BLK, 0, stream>>>(p);
+    if (p.logits) {
+        const int64_t rows = ncell * Po;
+        k_policy_from_logits<G><<<(int)((rows + WARPS - 1) / WARPS), BLK, 0, stream>>>(p);
+    }
+    return b200rl_check_launch("k_make_batch");
+}
+
+}  // namespace
+
+#define DISPATCH_GAME(game, EXPR)                                                       \
+    switch (game) {                                                                     \
+        case B200RL_GAME_TICTACTOE: { using G = TicTacToeGame<false>; EXPR; } break;     \
+        case B200RL_GAME_PARALLEL_TICTACTOE: { using G = TicTacToeGame<true>; EXPR; } break; \
+        case B200RL_GAME_GEISTER: { using G = GeisterGame<false>; EXPR; } break;         \
+        case B200RL_GAME_CIGEISTER: { using G = GeisterGame<true>; EXPR; } break;        \
+        default:                                                                        \
+            b200rl_set_error("unknown game id %d", game);                               \
+            return B200RL_ERR_ARG;                                                      \
+    }
+
+extern "C" int b200rl_env_step_record(int game, void* state, int64_t N, const int32_t* actions,
+                                      const int32_t* selected, const int32_t* both, int auto_reset, void* traj,
+                                      int64_t D, uint64_t it, int32_t* ep_table, int64_t E, uint64_t* counters,
+                                      uint8_t* out_terminal, void* stream) {
+    B200RL_REQUIRE(state && actions && traj && D >= 1, "env_step_record: null state/actions/traj or D < 1");
+    B200RL_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)traj % 16) == 0, "env_step_record: 16-byte alignment");
+    B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_step_record: episode table needs E >= 1 and counters");
+    if (N <= 0) return B200RL_OK;
+    DISPATCH_GAME(game, (k_step_record<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(
+                            (uint32_t*)state, N, actions, selected, both, auto_reset, (uint4*)traj, D, it, ep_table,
+                            E, (unsigned long long*)counters, out_terminal)));
+    return b200rl_check_launch("k_step_record");
+}
+
+extern "C" int b200rl_make_batch(int game, const void* traj, int64_t D, int64_t N, const float* values,
+                                 const float* logits, const int32_t* windows, int64_t B, int64_t T, int mode,
+                                 int obs_all, const float* ret_table, int64_t ret_len, float* obs_main,
+                                 float* obs_scalar, float* policy, float* amask, int64_t* action, float* value,
+                                 float* reward, float* ret, float* outcome, float* emask, float* tmask, float* omask,
+                                 float* progress, void* stream) {
+    B200RL_REQUIRE(traj && windows && D >= 1 && N >= 1, "make_batch: null trajectory ring / windows");
+    B200RL_REQUIRE(mode >= 0 && mode <= 2, "make_batch: mode must be 0 (turn), 1 (all players) or 2 (solo)");
+    B200RL_REQUIRE(T >= 1 && B >= 0, "make_batch: bad B/T");
+    B200RL_REQUIRE(obs_main && policy && amask && action && value && reward && ret && outcome && emask && tmask &&
+                       omask && progress, "make_batch: null output");
+    B200RL_REQUIRE(ret_table && ret_len >= 1, "make_batch: null return table");
+    B200RL_REQUIRE(((uintptr_t)obs_main % 16) == 0 && ((uintptr_t)policy % 16) == 0 && ((uintptr_t)amask % 16) == 0 &&
+                       ((uintptr_t)obs_scalar % 16) == 0, "make_batch: outputs must be 16-byte aligned");
+    if (B == 0) return B200RL_OK;
+    BatchParams p;
+    p.traj = (const uint4*)traj; p.D = D; p.N = N; p.values = values; p.logits = logits; p.win = windows;
+    p.ret_table = ret_table; p.ret_len = (int)ret_len; p.B = B; p.T = (int)T; p.mode = mode; p.obs_all = obs_all;
+    p.obs_main = obs_main; p.obs_scalar = obs_scalar; p.policy = policy; p.amask = amask;
+    p.action = (long long*)action; p.value = value; p.reward = reward; p.ret = ret; p.outcome = outcome;
+    p.emask = emask; p.tmask = tmask; p.omask = omask; p.progress = progress;
+    DISPATCH_GAME(game, return launch_make_batch<G>(p, (cudaStream_t)stream));
+    return B200RL_OK;
+}
+
+extern "C" int b200rl_pad_stack(const void* src, const int64_t* offsets, const void* fill_rows, uint32_t fill_bits,
+                                void* out, int64_t B, int64_t T, int64_t row_words, void* stream) {
+    B200RL_REQUIRE(offsets && out && B >= 0 && T >= 1 && row_words >= 1, "pad_stack: bad arguments");
+    const int64_t n = B * T * row_words;
+    if (n == 0) return B200RL_OK;
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    k_pad_stack<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const uint32_t*)src, offsets,
+                                                               (const uint32_t*)fill_rows, fill_bits, (uint32_t*)out,
+                                                               B, T, row_words);
+    return b200rl_check_launch("k_pad_stack");
+}

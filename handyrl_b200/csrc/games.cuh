@@ -33,6 +33,7 @@ struct TicTacToeGame {
     };
     static constexpr int A = 9, LW = 1, OBITS = 27, OW = 1, SBITS = 0, LMAX = 9, STATE_U32 = 1, PLAYERS = 2;
     static constexpr bool HAS_REWARD = false;
+    static constexpr bool SIMULTANEOUS = PARALLEL;  // both players act every ply
     static constexpr int MAX_STEPS = 9;
 
     __device__ __forceinline__ static State load(const uint32_t* __restrict__ st, int64_t N, int64_t i) {
@@ -149,6 +150,7 @@ struct GeisterGame {
     };
     static constexpr int A = 214, LW = 7, OBITS = 252, OW = 8, SBITS = 18, LMAX = 70, STATE_U32 = 16, PLAYERS = 2;
     static constexpr bool HAS_REWARD = true;
+    static constexpr bool SIMULTANEOUS = false;
     static constexpr int MAX_STEPS = 202;
 
     __device__ __forceinline__ static State load(const uint32_t* __restrict__ st, int64_t N, int64_t i) {

@@ -1,0 +1,165 @@
+"""Batched self-play on the GPU — the device counterpart of `handyrl/generation.py`.
+
+The reference `Generator.generate` (handyrl/generation.py:20-88) plays ONE game per call
+in a worker process and returns an episode dict whose moments are bz2-pickled.  Here N
+games advance together on one GPU and their moments stay in HBM as a ring of 32-byte
+records (`TrajectoryStore`); an episode is the same dict (`args, steps, outcome, moment`)
+whose `moment` is a `DeviceMoments` handle instead of a list of compressed blobs, so the
+reference's `select_episode` slicing (handyrl/train.py:294-301) works on it unchanged and
+`handyrl_b200.train.make_batch` gathers windows straight from the ring.
+"""
+import bz2
+import pickle
+
+import numpy as np
+import torch
+
+from . import _lib
+from .engine import BatchedEnv, _ptr
+
+
+class TrajectoryStore:
+    """Ring of per-ply records for N game slots: [D][2][N] uint4 (32 B per ply and slot),
+    plus the finished-episode table and counters filled by the kernels."""
+
+    def __init__(self, env, depth=None, max_episodes=1 << 16, record_values=False, record_logits=False):
+        self.env = env
+        self.N = env.N
+        self.D = int(depth or max(2 * env.max_steps + 64, 64))
+        dev = env.device
+        self.traj = torch.zeros(self.D, 2, self.N, 4, dtype=torch.int32, device=dev)
+        self.E = int(max_episodes)
+        self.ep_table = torch.zeros(self.E, 4, dtype=torch.int32, device=dev)
+        self.counters = torch.zeros(8, dtype=torch.int64, device=dev)
+        self.values = torch.zeros(self.D, self.N, 2, dtype=torch.float32, device=dev) if record_values else None
+        self.logits = torch.zeros(self.D, self.N, env.A, dtype=torch.float32, device=dev) if record_logits else None
+        self.it = 0            # next ring iteration to be written
+        self._ep_read = 0      # episode-table cursor already handed out
+
+
+class DeviceMoments:
+    """`episode['moment']` of a device-resident episode: plies [0, steps) of one game slot,
+    ply k stored at ring iteration first_it + k.  Slicing returns the handle itself, which is
+    what `select_episode` (handyrl/train.py:296-299) needs."""
+
+    def __init__(self, store, slot, first_it, steps):
+        self.store, self.slot, self.first_it, self.steps = store, int(slot), int(first_it), int(steps)
+
+    def __getitem__(self, item):
+        return self
+
+    def __len__(self):
+        return self.steps
+
+    def alive(self):
+        """True while the ring has not wrapped over this episode."""
+        return self.store.it - self.first_it <= self.store.D
+
+
+WIN_OUTCOME = {0: (0, 0), 1: (1, -1), 2: (-1, 1), 3: (0, 0)}
+
+
+class BatchGenerator:
+    """N concurrent self-play games on one GPU (one process per GPU; shard by `game_id_base`)."""
+
+    def __init__(self, game, n_games, device="cuda", seed=0, game_id_base=0, depth=None, max_episodes=1 << 16,
+                 record_values=False, record_logits=False, args=None):
+        self.env = BatchedEnv(game, n_games, device=device)
+        self.store = TrajectoryStore(self.env, depth, max_episodes, record_values, record_logits)
+        self.seed, self.game_id_base = int(seed), int(game_id_base)
+        self.args = args or {}
+
+    # -- epoch-0 policy: everything on the device ---------------------------------
+    def rollout(self, n_plies, waves=None, out_action=None):
+        """n_plies plies per game with the uniform (RandomModel) policy, auto-reset."""
+        st = self.store
+        assert self.env.it == st.it
+        self.env.rollout(n_plies, seed=self.seed, game_id_base=self.game_id_base, waves=waves, traj=st.traj,
+                         ep_table=st.ep_table, counters=st.counters, out_action=out_action)
+        st.it = self.env.it
+
+    # -- caller-chosen actions (policy network in PyTorch, tape replay) -------------
+    def step(self, actions, selected=None, both=None, values=None, logits=None, auto_reset=True):
+        """One recorded ply.  actions (N,) int32, <0 = slot idle.  `values` (N,2) / `logits` (N,A)
+        are stored beside the ring when the store records them.  Returns terminal (N,) uint8."""
+        env, st = self.env, self.store
+        a, s, b = env._i32(actions), env._i32(selected), env._i32(both)
+        k = st.it % st.D
+        if st.values is not None and values is not None:
+            st.values[k].copy_(values)
+        if st.logits is not None and logits is not None:
+            st.logits[k].copy_(logits)
+        term = torch.empty(env.N, dtype=torch.uint8, device=env.device)
+        with torch.cuda.device(env.device):
+            _lib.call("b200rl_env_step_record", env.game, env._st(), env.N, _ptr(a), _ptr(s), _ptr(b),
+                      1 if auto_reset else 0, _ptr(st.traj), st.D, st.it, _ptr(st.ep_table), st.E,
+                      _ptr(st.counters), _ptr(term), env._stream())
+        st.it += 1
+        env.it = st.it
+        return term
+
+    # -- finished episodes ------------------------------------------------------------
+    def stats(self):
+        c = self.store.counters.cpu().numpy()
+        return {"episodes": int(c[0]), "env_steps": int(c[1]), "wins0": int(c[2]), "wins1": int(c[3]),
+                "draws": int(c[4])}
+
+    def episodes(self):
+        """Episodes finished since the last call, in reference form
+        `{'args', 'steps', 'outcome', 'moment'}` (generation.py:79-86) with a DeviceMoments handle."""
+        st = self.store
+        cur = int(st.counters[5].item())
+        lo = max(self._read_cursor(), cur - st.E)
+        out = []
+        if cur > lo:
+            idx = torch.arange(lo, cur, device=st.ep_table.device) % st.E
+            rows = st.ep_table[idx].cpu().numpy()
+            for slot, sw, it_lo, it_hi in rows:
+                steps, win = int(sw) & 0xFFFF, (int(sw) >> 16) & 3
+                end_it = (int(np.uint32(it_lo)) | (int(np.uint32(it_hi)) << 32))
+                o = WIN_OUTCOME[win]
+                out.append({"args": self.args, "steps": steps, "outcome": {0: o[0], 1: o[1]},
+                            "moment": DeviceMoments(st, slot, end_it - steps + 1, steps), "win": win})
+        st._ep_read = cur
+        return out
+
+    def _read_cursor(self):
+        return self.store._ep_read
+
+
+def export_episode(ep, args):
+    """Device episode -> the reference wire format (generation.py:79-86): moments re-encoded on the GPU,
+    pickled and bz2-compressed in blocks of args['compress_steps'].  RandomModel semantics: zero logits and
+    zero values unless the store recorded them."""
+    from .train import make_batch  # local import: train imports this module
+    steps = ep["steps"]
+    win = {"args": ep["args"], "outcome": ep["outcome"], "moment": ep["moment"], "base": 0, "start": 0,
+           "end": steps, "total": steps, "win": ep.get("win")}
+    a = dict(args)
+    a.update(turn_based_training=True, observation=False, forward_steps=steps)
+    b = make_batch([win], a)
+    cpu = lambda t: t[0].cpu().numpy()
+    obs = b["observation"]
+    pol, am, act = cpu(b["policy"]), cpu(b["action_mask"]), cpu(b["action"])
+    val, rew, ret, tm = cpu(b["value"]), cpu(b["reward"]), cpu(b["return"]), cpu(b["turn_mask"])
+    env = ep["moment"].store.env
+    moments = []
+    keys = ["observation", "policy", "action_mask", "action", "value", "reward", "return"]
+    for t in range(steps):
+        m = {k: {0: None, 1: None} for k in keys}
+        turn = [p for p in (0, 1) if tm[t, p, 0] > 0]
+        for p in turn[:1]:
+            if isinstance(obs, dict):
+                m["observation"][p] = {k: v[0, t, 0].cpu().numpy() for k, v in obs.items()}
+            else:
+                m["observation"][p] = obs[0, t, 0].cpu().numpy()
+            m["policy"][p], m["action_mask"][p], m["action"][p] = pol[t, 0], am[t, 0], int(act[t, 0, 0])
+            m["value"][p] = val[t, p]
+        for p in (0, 1):
+            m["reward"][p] = float(rew[t, p, 0]) if env.has_reward else None
+            m["return"][p] = float(ret[t, p, 0])
+        m["turn"] = turn
+        moments.append(m)
+    cs = args["compress_steps"]
+    return {"args": ep["args"], "steps": steps, "outcome": ep["outcome"],
+            "moment": [bz2.compress(pickle.dumps(moments[i:i + cs])) for i in range(0, steps, cs)]}

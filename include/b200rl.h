@@ -157,6 +157,60 @@ int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_plies, uint64
                        int64_t waves, void* traj, int64_t D, int32_t* ep_table, int64_t E, uint64_t* counters,
                        void* stream);
 
+/* ------------------------------------------------------------------ */
+/* Part 2: episode -> batch assembly — handyrl/train.py:33-133          */
+/* ------------------------------------------------------------------ */
+
+/*
+ * One ply driven by caller-chosen actions (net-in-the-loop self-play, tape replay):
+ * Environment.step() as in b200rl_env_step, plus the 32-byte trajectory record of the
+ * ply (pre-move state, action, episode flags) written to ring slot it % D, and the
+ * episode-table / counter bookkeeping of b200rl_env_rollout.  A slot with actions[i] < 0
+ * does not move.  `both` (N,2) carries both players' chosen actions for
+ * ParallelTicTacToe (make_batch needs them), else NULL.  With auto_reset a finished
+ * game is restarted before the ply (generation.py:27).
+ */
+int b200rl_env_step_record(int game, void* state, int64_t N, const int32_t* actions, const int32_t* selected,
+                           const int32_t* both, int auto_reset, void* traj, int64_t D, uint64_t it,
+                           int32_t* ep_table, int64_t E, uint64_t* counters, uint8_t* out_terminal, void* stream);
+
+enum { B200RL_BATCH_TURN = 0, B200RL_BATCH_ALL = 1, B200RL_BATCH_SOLO = 2 };
+
+/*
+ * make_batch(episodes, args) (handyrl/train.py:33-133) over windows of the device
+ * trajectory ring.
+ *   traj     : [D][2][N] uint4 ring written by b200rl_env_rollout / b200rl_env_step_record
+ *   values   : [D][N][2] fp32 value estimates recorded beside the ring, or NULL (RandomModel: 0)
+ *   logits   : [D][N][A] fp32 behaviour logits, or NULL (RandomModel: zero logits)
+ *   windows  : (B,8) int32 {slot, first_it lo, first_it hi, len = end-start, start, total steps,
+ *              winner code, solo player}; first_it is the ring iteration of ply `start`
+ *   T        : args['forward_steps']; rows t >= len are padded exactly like train.py:92-104
+ *   mode     : TURN = turn_based_training and not observation (train.py:64-68);
+ *              ALL  = turn_based_training and observation (both players, train.py:69-73);
+ *              SOLO = not turn_based_training (one player per episode, train.py:57-58)
+ *   obs_all  : args['observation'] (every player observes every ply)
+ *   ret_table: ret_table[m] = discounted return of a ply with m plies left (generation.py:73-77,
+ *              accumulated in double by the caller, rounded to fp32)
+ * Outputs are the tensors of the returned dict, contiguous, shapes as in train.py:109-133
+ * with Po = 2 for ALL else 1 and Pv = 1 for SOLO else 2:
+ *   obs_main (B,T,Po,...) obs_scalar (B,T,Po,18)|NULL policy/amask (B,T,Po,A) action (B,T,Po,1) int64
+ *   value/reward/ret/tmask/omask (B,T,Pv,1) outcome (B,1,Pv,1) emask (B,T,1,1) progress (B,T,1)
+ */
+int b200rl_make_batch(int game, const void* traj, int64_t D, int64_t N, const float* values, const float* logits,
+                      const int32_t* windows, int64_t B, int64_t T, int mode, int obs_all, const float* ret_table,
+                      int64_t ret_len, float* obs_main, float* obs_scalar, float* policy, float* amask,
+                      int64_t* action, float* value, float* reward, float* ret, float* outcome, float* emask,
+                      float* tmask, float* omask, float* progress, void* stream);
+
+/*
+ * Padding + stacking step of make_batch (train.py:92-122) for episodes that were decoded on the
+ * host (reference wire format): `src` holds the windows of all B episodes back to back, rows of
+ * `row_words` 32-bit words, episode b owning rows offsets[b]..offsets[b+1]; out is (B, T, row)
+ * with rows t >= length filled from fill_rows[b] (B,row) when given, else with fill_bits.
+ */
+int b200rl_pad_stack(const void* src, const int64_t* offsets, const void* fill_rows, uint32_t fill_bits, void* out,
+                     int64_t B, int64_t T, int64_t row_words, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -114,6 +114,82 @@ def gen_games():
         print("tape_%s.npz: %d games, %d states" % (name, n_games, len(out['game'])))
 
 
+BATCH_CASES = [
+    # name, env module, B, T, compress_steps, turn_based_training, observation, episodes
+    ('ttt_turn', 'tictactoe', 12, 4, 4, True, False, 10),
+    ('ttt_long', 'tictactoe', 6, 16, 4, True, False, 6),
+    ('ttt_all', 'tictactoe', 8, 5, 2, True, True, 8),
+    ('ttt_solo', 'tictactoe', 8, 6, 4, False, False, 8),
+    ('pttt_solo', 'parallel_tictactoe', 10, 5, 4, False, False, 8),
+    ('pttt_turn', 'parallel_tictactoe', 6, 6, 4, True, False, 6),
+    ('geister_turn', 'geister', 8, 16, 4, True, False, 4),
+    ('geister_all', 'geister', 4, 8, 4, True, True, 3),
+    ('cigeister_turn', 'ci_geister', 4, 8, 4, True, False, 3),
+    ('geister_solo', 'geister', 4, 8, 4, False, False, 3),
+]
+
+
+def gen_batch():
+    import importlib
+    import pickle
+    import random
+    from handyrl.generation import Generator
+    from handyrl.model import ModelWrapper, RandomModel
+    from handyrl.train import make_batch
+    from handyrl_b200.train import select_episode
+
+    cases = {}
+    for ci, (name, envname, B, T, cs, tbt, obs, n_ep) in enumerate(BATCH_CASES):
+        mod = importlib.import_module('handyrl.envs.' + envname)
+        env = mod.Environment()
+        args = {'turn_based_training': tbt, 'observation': obs, 'gamma': 0.8, 'forward_steps': T,
+                'compress_steps': cs, 'maximum_episodes': 1000}
+        gen = Generator(env, args)
+        models = {p: ModelWrapper(RandomModel(env)) for p in env.players()}
+        random.seed(500 + ci)
+        episodes, tapes = [], []
+        for _ in range(n_ep):
+            ep = gen.generate(models, {})
+            moments = sum([pickle.loads(__import__('bz2').decompress(ms)) for ms in ep['moment']], [])
+            if envname == 'parallel_tictactoe':
+                acts = [[m['action'][0], m['action'][1]] for m in moments]
+                sel = [0 if color == env.BLACK else 1 for color, _ in env.record]
+                landed = [a for _, a in env.record]
+            else:
+                landed = [m['action'][m['turn'][0]] for m in moments]
+                acts = [[a, a] for a in landed]
+                sel = [0] * len(landed)
+            tapes.append({'actions': np.asarray(landed, np.int32), 'both': np.asarray(acts, np.int32),
+                          'sel': np.asarray(sel, np.int32), 'steps': ep['steps'],
+                          'outcome': [ep['outcome'][0], ep['outcome'][1]]})
+            episodes.append(ep)
+        rng = random.Random(900 + ci)
+        picks = []
+        for _ in range(B):
+            w = select_episode(episodes, args, rng)
+            idx = [i for i, e in enumerate(episodes) if e['outcome'] is w['outcome'] and e['steps'] == w['total']
+                   and e['moment'][w['base'] // cs:] [:len(w['moment'])] == w['moment']][0]
+            picks.append((idx, w))
+        random.seed(77 + ci)
+        out = make_batch([w for _, w in picks], args)
+        random.seed(77 + ci)
+        solo = [random.choice([0, 1]) for _ in picks] if not tbt else [0] * B
+        flat = {}
+        for k, v in out.items():
+            if isinstance(v, dict):
+                for kk, vv in v.items():
+                    flat['observation.' + kk] = vv.numpy()
+            else:
+                flat[k] = v.numpy()
+        cases[name] = {'env': envname, 'args': args, 'tapes': tapes,
+                       'windows': [(idx, w['start'], w['end'], w['total']) for idx, w in picks],
+                       'ep_minimum': [w for _, w in picks], 'solo': solo, 'seed': 77 + ci, 'out': flat}
+        print(name, {k: v.shape for k, v in flat.items() if k in ('policy', 'value')})
+    with open(os.path.join(GOLD, "batch_cases.pkl"), "wb") as f:
+        pickle.dump(cases, f, protocol=4)
+    print("batch_cases.pkl:", os.path.getsize(os.path.join(GOLD, "batch_cases.pkl")), "bytes")
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     os.makedirs(GOLD, exist_ok=True)
