@@ -186,6 +186,13 @@ struct GeisterGame {
         o1 = s.win == 1 ? -1.f : (s.win == 2 ? 1.f : 0.f);
     }
 
+    // piece_cnt[k] of the reference.  `spare` holds four signed byte corrections that are non-zero only
+    // in network-match mirror environments, where update() rewrites a captured piece's type on the
+    // board without touching piece_cnt (geister.py:416-424).
+    __device__ __forceinline__ static int cnt(const State& s, int k) {
+        return __popcll(s.bb[k]) + (int)(int8_t)((s.spare >> (8 * k)) & 0xFF);
+    }
+
     __device__ __forceinline__ static void pos_replace(State& s, uint32_t cell, uint32_t newv) {
         const uint32_t rep = cell * 0x01010101u, nv = newv * 0x01010101u;
 #pragma unroll
@@ -246,7 +253,7 @@ struct GeisterGame {
             if (cap >= 0) {  // geister.py:376-385
                 s.bb[cap] &= ~tbit;
                 pos_replace(s, to, 0xFF);
-                if (s.bb[cap] == 0) s.win = ((cap & 1) == 0) ? (c + 1) : (2 - c);
+                if (cnt(s, cap) == 0) s.win = ((cap & 1) == 0) ? (c + 1) : (2 - c);
                 captured = (cap & 1) + 1;
             }
             s.bb[piece] = (s.bb[piece] & ~fbit) | tbit;
@@ -343,8 +350,9 @@ struct GeisterGame {
         const int vc = turn_view ? tp : 1 - tp;
         const int oc = 1 - vc;
         const uint64_t cb = s.bb[vc * 2], cr = s.bb[vc * 2 + 1], obl = s.bb[oc * 2], ore = s.bb[oc * 2 + 1];
-        scalar = (vc == 0 ? 1u : 0u) | (turn_view ? 2u : 0u) | (onehot4(__popcll(cb)) << 2) |
-                 (onehot4(__popcll(cr)) << 6) | (onehot4(__popcll(obl)) << 10) | (onehot4(__popcll(ore)) << 14);
+        scalar = (vc == 0 ? 1u : 0u) | (turn_view ? 2u : 0u) | (onehot4(cnt(s, vc * 2)) << 2) |
+                 (onehot4(cnt(s, vc * 2 + 1)) << 6) | (onehot4(cnt(s, oc * 2)) << 10) |
+                 (onehot4(cnt(s, oc * 2 + 1)) << 14);
         const bool show = CI || (view == B200RL_VIEW_NONE);
         uint64_t pl[7] = {G_M36, cb | cr, obl | ore, cb, cr, show ? obl : 0ull, show ? ore : 0ull};
         if (vc == 1) {

@@ -128,3 +128,16 @@ def test_full_size_make_batch_properties():
     assert bool((b['observation']['board'][~live] == 0).all())
     assert bool((b['progress'][~live] == 1).all()) and bool((b['progress'][live] < 1).all())
     assert bool((b['value'][~live] == b['outcome'].expand(-1, 16, -1, -1)[~live]).all())
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_reference_format_episodes_match_reference(cases, name):
+    """the drop-in signature on the reference's own wire format (bz2-pickled moments)"""
+    from handyrl_b200.train import make_batch
+    c = cases[name]
+    random.seed(c['seed'])
+    out = _flatten(make_batch(c['ep_minimum'], c['args']))
+    assert set(out) == set(c['out'])
+    for k, ref in c['out'].items():
+        assert out[k].shape == ref.shape and out[k].dtype == ref.dtype, (k, out[k].shape, ref.shape, out[k].dtype)
+        np.testing.assert_array_equal(out[k], ref, err_msg=k)
