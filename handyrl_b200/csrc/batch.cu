@@ -86,19 +86,29 @@ struct BatchParams {
     float *value, *reward, *ret, *outcome, *emask, *tmask, *omask, *progress;
 };
 
-// per-warp staging for 32 cells x up to 2 observed players
+// per-warp staging for 32 cells x up to 2 observed players: flat bit strings (emit.cuh)
 template <class G>
 struct BatchStage {
-    uint32_t obs[64 * G::OW];
-    uint32_t legal[64 * G::LW];   // 1 = legal                (action_mask: 0 / 1e32)
-    uint32_t illegal[64 * G::LW]; // 1 = illegal on a live row (policy: -1e32 / 0)
-    uint32_t scalar[64];
+    uint32_t obs[flat_words(64, G::OBITS)];
+    uint32_t legal[flat_words(64, G::A)];     // 1 = legal                (action_mask: 0 / 1e32)
+    uint32_t illegal[flat_words(64, G::A)];   // 1 = illegal on a live row (policy: -1e32 / 0)
+    uint32_t scalar[flat_words(64, G::SBITS > 0 ? G::SBITS : 1)];
+};
+
+template <class G>
+struct BatchCta {
+    float4 tbl_obs[16], tbl_amask[16], tbl_policy[16];
+    BatchStage<G> w[WARPS];
 };
 
 template <class G>
 __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
-    __shared__ BatchStage<G> stage[WARPS];
-    BatchStage<G>& st = stage[threadIdx.x >> 5];
+    __shared__ BatchCta<G> cta;
+    nibble_table_init(cta.tbl_obs, 0.f, 1.f, threadIdx.x);
+    nibble_table_init(cta.tbl_amask, 1e32f, 0.f, threadIdx.x);
+    nibble_table_init(cta.tbl_policy, 0.f, -1e32f, threadIdx.x);
+    __syncthreads();
+    BatchStage<G>& st = cta.w[threadIdx.x >> 5];
     const int lane = threadIdx.x & 31;
     const int64_t ncell = p.B * p.T;
     const int64_t c0 = (blockIdx.x * (int64_t)WARPS + (threadIdx.x >> 5)) * 32;
@@ -192,28 +202,40 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
             else { p.outcome[b * 2] = oc0; p.outcome[b * 2 + 1] = oc1; }
         }
     }
-    // ---- stage bits, then stream the big tensors ----
-    for (int q = 0; q < Po; ++q) {
-        const int si = lane * Po + q;
-#pragma unroll
-        for (int k = 0; k < G::OW; ++k) st.obs[si * G::OW + k] = ob[q][k];
-#pragma unroll
-        for (int k = 0; k < G::LW; ++k) {
-            st.legal[si * G::LW + k] = lg[q][k];
-            st.illegal[si * G::LW + k] = il[q][k];
+    // ---- pack bits into the warp's flat strings, then stream the big tensors ----
+    constexpr int SB = G::SBITS > 0 ? G::SBITS : 1;
+    const int ng = nc * Po;
+    const bool rnd_policy = p.logits == nullptr;
+    if (valid) {
+        for (int q = 0; q < Po; ++q) {
+            const int row = lane * Po + q;
+            const bool last = row == ng - 1;
+            flat_clear_row<G::OBITS>(st.obs, row, last);
+            if (G::SBITS > 0) flat_clear_row<SB>(st.scalar, row, last);
+            flat_clear_row<G::A>(st.legal, row, last);
+            if (rnd_policy) flat_clear_row<G::A>(st.illegal, row, last);
         }
-        st.scalar[si] = sc[q];
     }
     __syncwarp();
-    const int ng = nc * Po;
-    emit_tile_f32<G::OBITS, G::OW>(st.obs, p.obs_main + c0 * Po * G::OBITS, ng, lane, 0.f, 1.f);
-    if (G::SBITS > 0)
-        emit_tile_f32<(G::SBITS > 0 ? G::SBITS : 1), 1>(st.scalar, p.obs_scalar + c0 * Po * G::SBITS, ng, lane, 0.f,
-                                                        1.f);
-    emit_tile_f32<G::A, G::LW>(st.legal, p.amask + c0 * Po * G::A, ng, lane, 1e32f, 0.f);
-    if (p.logits == nullptr) {
+    if (valid) {
+        for (int q = 0; q < Po; ++q) {
+            const int row = lane * Po + q;
+            flat_put<G::OBITS, G::OW>(st.obs, row, ob[q]);
+            if (G::SBITS > 0) {
+                const uint32_t s1[1] = {sc[q]};
+                flat_put<SB, 1>(st.scalar, row, s1);
+            }
+            flat_put<G::A, G::LW>(st.legal, row, lg[q]);
+            if (rnd_policy) flat_put<G::A, G::LW>(st.illegal, row, il[q]);
+        }
+    }
+    __syncwarp();
+    emit_flat_f32<G::OBITS>(st.obs, cta.tbl_obs, p.obs_main + c0 * Po * G::OBITS, ng, lane, 0.f, 1.f);
+    if (G::SBITS > 0) emit_flat_f32<SB>(st.scalar, cta.tbl_obs, p.obs_scalar + c0 * Po * G::SBITS, ng, lane, 0.f, 1.f);
+    emit_flat_f32<G::A>(st.legal, cta.tbl_amask, p.amask + c0 * Po * G::A, ng, lane, 1e32f, 0.f);
+    if (rnd_policy) {
         // RandomModel: policy = 0 - action_mask on live turn rows, 0 elsewhere (train.py:61,70,94)
-        emit_tile_f32<G::A, G::LW>(st.illegal, p.policy + c0 * Po * G::A, ng, lane, 0.f, -1e32f);
+        emit_flat_f32<G::A>(st.illegal, cta.tbl_policy, p.policy + c0 * Po * G::A, ng, lane, 0.f, -1e32f);
     }
 }
 
@@ -256,6 +278,54 @@ k_pad_stack(const uint32_t* __restrict__ src, const int64_t* __restrict__ off, c
         else v = fill_rows ? fill_rows[b * row + j] : fill;
         out[e] = v;
     }
+}
+
+// Batcher.select_episode (handyrl/train.py:284-302) for B windows at once, over the finished-episode
+// table the rollout kernels fill.  The replay buffer `self.episodes` is the last
+// L = min(finished, E, maximum_episodes) rows of the table in finishing order (index 0 = oldest);
+// a row whose first ply has already been overwritten in the trajectory ring is skipped like a rejected
+// draw.  Draws come from the counter RNG keyed (seed, window b, draw0 + 4*try + j).
+__global__ void __launch_bounds__(128)
+k_select_windows(const int32_t* __restrict__ ep_table, int64_t E, const unsigned long long* __restrict__ counters,
+                 int64_t maximum_episodes, int forward_steps, uint64_t seed, uint64_t draw0, uint64_t it_now,
+                 int64_t D, int32_t* __restrict__ out, int64_t B) {
+    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const unsigned long long cursor = counters[5];
+    int64_t L = (int64_t)min(cursor, (unsigned long long)E);
+    int32_t* w = out + b * 8;
+    if (L <= 0) {  // nothing finished yet: an empty window (all rows padded)
+        w[0] = 0; w[1] = 0; w[2] = 0; w[3] = 0; w[4] = 0; w[5] = 1; w[6] = 3; w[7] = 0;
+        return;
+    }
+    const int64_t n_draw = min(L, maximum_episodes);
+    int32_t slot = 0, steps = 1, win = 3;
+    uint64_t end_it = 0;
+    uint32_t r2 = 0, r3 = 0;
+    for (int tr = 0; tr < 64; ++tr) {
+        const uint64_t c = draw0 + 4ull * (uint64_t)tr;
+        const uint32_t r0 = b200rl_rand32(seed, (uint64_t)b, c), r1 = b200rl_rand32(seed, (uint64_t)b, c + 1);
+        r2 = b200rl_rand32(seed, (uint64_t)b, c + 2);
+        r3 = b200rl_rand32(seed, (uint64_t)b, c + 3);
+        int64_t ep_idx = (int64_t)(((unsigned long long)r0 * (unsigned long long)n_draw) >> 32);  // train.py:286
+        const double accept = 1.0 - (double)(L - 1 - ep_idx) / (double)maximum_episodes;         // train.py:287
+        const bool last_try = tr == 63;
+        if (last_try) ep_idx = L - 1;
+        const int32_t* e = ep_table + (int64_t)((cursor - (unsigned long long)L + (unsigned long long)ep_idx) %
+                                                 (unsigned long long)E) * 4;
+        slot = e[0];
+        steps = e[1] & 0xFFFF;
+        win = (e[1] >> 16) & 3;
+        end_it = (uint64_t)(uint32_t)e[2] | ((uint64_t)(uint32_t)e[3] << 32);
+        const bool alive = it_now - (end_it + 1 - (uint64_t)steps) <= (uint64_t)D;
+        if (last_try || (alive && (double)r1 * (1.0 / 4294967296.0) < accept)) break;  // train.py:288
+    }
+    const int cand = 1 + max(0, steps - forward_steps);                                  // train.py:291
+    const int st = (int)(((unsigned long long)r2 * (unsigned long long)cand) >> 32);      // train.py:292
+    const int ed = min(st + forward_steps, steps);                                       // train.py:293
+    const uint64_t first = end_it + 1 - (uint64_t)steps + (uint64_t)st;
+    w[0] = slot; w[1] = (int32_t)(uint32_t)first; w[2] = (int32_t)(uint32_t)(first >> 32);
+    w[3] = ed - st; w[4] = st; w[5] = steps; w[6] = win; w[7] = (int32_t)(r3 >> 31);  // solo player, train.py:57-58
 }
 
 inline int grid_for(int64_t n) { return (int)((n + BLK - 1) / BLK); }
@@ -323,6 +393,19 @@ extern "C" int b200rl_make_batch(int game, const void* traj, int64_t D, int64_t 
     p.emask = emask; p.tmask = tmask; p.omask = omask; p.progress = progress;
     DISPATCH_GAME(game, return launch_make_batch<G>(p, (cudaStream_t)stream));
     return B200RL_OK;
+}
+
+extern "C" int b200rl_select_windows(const int32_t* ep_table, int64_t E, const uint64_t* counters,
+                                     int64_t maximum_episodes, int64_t forward_steps, uint64_t seed, uint64_t draw0,
+                                     uint64_t it_now, int64_t D, int32_t* out_windows, int64_t B, void* stream) {
+    B200RL_REQUIRE(ep_table && counters && out_windows, "select_windows: null pointer");
+    B200RL_REQUIRE(E >= 1 && D >= 1 && maximum_episodes >= 1 && forward_steps >= 1 && B >= 0,
+                   "select_windows: bad E/D/maximum_episodes/forward_steps/B");
+    if (B == 0) return B200RL_OK;
+    k_select_windows<<<(int)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        ep_table, E, (const unsigned long long*)counters, maximum_episodes, (int)forward_steps, seed, draw0, it_now, D,
+        out_windows, B);
+    return b200rl_check_launch("k_select_windows");
 }
 
 extern "C" int b200rl_pad_stack(const void* src, const int64_t* offsets, const void* fill_rows, uint32_t fill_bits,

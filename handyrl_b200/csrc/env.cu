@@ -10,15 +10,28 @@
 
 namespace {
 
-constexpr int BLK = 128;           // threads per CTA = games per CTA
+constexpr int BLK = 64;            // threads per CTA = games per CTA: 65,536 games -> 1024 CTAs, 6.9 per SM
 constexpr int WARPS = BLK / 32;
 
-// shared staging per warp: observation bits, legal bits, scalar bits for 32 games
+// Shared staging: per warp the flat bit strings of its 32 games (emit.cuh), per CTA the
+// nibble -> float4 tables of the two value pairs that occur (0/1 and 1e32/0).
 template <class G>
 struct WarpStage {
-    uint32_t obs[32 * G::OW];
-    uint32_t legal[32 * G::LW];
-    uint32_t scalar[32];
+    uint32_t obs[flat_words(32, G::OBITS)];
+    uint32_t legal[flat_words(32, G::A)];
+    uint32_t scalar[flat_words(32, G::SBITS > 0 ? G::SBITS : 1)];
+};
+
+template <class G>
+struct CtaStage {
+    float4 tbl_obs[16];    // observation planes / scalars: bit -> 1.0f, else 0.0f
+    float4 tbl_amask[16];  // action_mask: legal bit -> 0.0f, else 1e32f (generation.py:50-51)
+    WarpStage<G> w[WARPS];
+    __device__ __forceinline__ void init() {
+        nibble_table_init(tbl_obs, 0.f, 1.f, threadIdx.x);
+        nibble_table_init(tbl_amask, 1e32f, 0.f, threadIdx.x);
+        __syncthreads();
+    }
 };
 
 template <class G>
@@ -87,35 +100,40 @@ __global__ void __launch_bounds__(BLK) k_info(const uint32_t* state, int64_t N, 
     out[4 * i + 3] = G::terminal(s) ? (o0 > 0 ? 1 : (o1 > 0 ? 2 : 3)) : 0;
 }
 
-// Stage this lane's bits, then let the warp stream the tile out.
+// Pack this lane's bits into the warp's flat strings, then let the warp stream the tile out.
 template <class G>
-__device__ __forceinline__ void emit_views(WarpStage<G>& st, const typename G::State& s, bool valid, int view,
-                                           int64_t g0, int ng, int lane, float* out_main, float* out_scalar,
-                                           float* out_amask, uint32_t* out_bits) {
-    uint32_t ob[G::OW], sc = 0, lm[G::LW];
-#pragma unroll
-    for (int k = 0; k < G::OW; ++k) ob[k] = 0;
-#pragma unroll
-    for (int k = 0; k < G::LW; ++k) lm[k] = 0;
+__device__ __forceinline__ void emit_views(CtaStage<G>& cta, int warp, const typename G::State& s, bool valid,
+                                           int view, int64_t g0, int ng, int lane, float* out_main,
+                                           float* out_scalar, float* out_amask, uint32_t* out_bits) {
+    WarpStage<G>& st = cta.w[warp];
+    constexpr int SB = G::SBITS > 0 ? G::SBITS : 1;
+    const bool want_obs = out_main || (G::SBITS > 0 && out_scalar);
+    const bool want_legal = out_amask || out_bits;
+    uint32_t ob[G::OW], sc[1] = {0}, lm[G::LW];
     if (valid) {
-        if (out_main || out_scalar) G::obs_bits(s, view, ob, sc);
-        if (out_amask || out_bits) G::legal_bits(s, lm);
-    }
-#pragma unroll
-    for (int k = 0; k < G::OW; ++k) st.obs[lane * G::OW + k] = ob[k];
-#pragma unroll
-    for (int k = 0; k < G::LW; ++k) st.legal[lane * G::LW + k] = lm[k];
-    st.scalar[lane] = sc;
-    if (out_bits && valid) {
-#pragma unroll
-        for (int k = 0; k < G::LW; ++k) out_bits[(g0 + lane) * G::LW + k] = lm[k];
+        if (want_obs) G::obs_bits(s, view, ob, sc[0]);
+        if (want_legal) G::legal_bits(s, lm);
+        const bool last = lane == ng - 1;
+        if (out_main) flat_clear_row<G::OBITS>(st.obs, lane, last);
+        if (G::SBITS > 0 && out_scalar) flat_clear_row<SB>(st.scalar, lane, last);
+        if (out_amask) flat_clear_row<G::A>(st.legal, lane, last);
     }
     __syncwarp();
-    if (out_main) emit_tile_f32<G::OBITS, G::OW>(st.obs, out_main + g0 * G::OBITS, ng, lane, 0.f, 1.f);
+    if (valid) {
+        if (out_main) flat_put<G::OBITS, G::OW>(st.obs, lane, ob);
+        if (G::SBITS > 0 && out_scalar) flat_put<SB, 1>(st.scalar, lane, sc);
+        if (out_amask) flat_put<G::A, G::LW>(st.legal, lane, lm);
+        if (out_bits) {
+#pragma unroll
+            for (int k = 0; k < G::LW; ++k) out_bits[(g0 + lane) * G::LW + k] = lm[k];
+        }
+    }
+    __syncwarp();
+    if (out_main) emit_flat_f32<G::OBITS>(st.obs, cta.tbl_obs, out_main + g0 * G::OBITS, ng, lane, 0.f, 1.f);
     if (G::SBITS > 0 && out_scalar)
-        emit_tile_f32<(G::SBITS > 0 ? G::SBITS : 1), 1>(st.scalar, out_scalar + g0 * G::SBITS, ng, lane, 0.f, 1.f);
+        emit_flat_f32<SB>(st.scalar, cta.tbl_obs, out_scalar + g0 * G::SBITS, ng, lane, 0.f, 1.f);
     // action_mask = 1e32 on illegal, 0 on legal (generation.py:50-51)
-    if (out_amask) emit_tile_f32<G::A, G::LW>(st.legal, out_amask + g0 * G::A, ng, lane, 1e32f, 0.f);
+    if (out_amask) emit_flat_f32<G::A>(st.legal, cta.tbl_amask, out_amask + g0 * G::A, ng, lane, 1e32f, 0.f);
     __syncwarp();
 }
 
@@ -123,7 +141,8 @@ template <class G>
 __global__ void __launch_bounds__(BLK) k_observe(const uint32_t* state, int64_t N, int view, const int32_t* views,
                                                  float* out_main, float* out_scalar, float* out_amask,
                                                  uint32_t* out_bits) {
-    __shared__ WarpStage<G> stage[WARPS];
+    __shared__ CtaStage<G> stage;
+    stage.init();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t g0 = (blockIdx.x * (int64_t)WARPS + warp) * 32;
     if (g0 >= N) return;
@@ -133,7 +152,7 @@ __global__ void __launch_bounds__(BLK) k_observe(const uint32_t* state, int64_t 
     G::reset(s);
     if (valid) s = G::load(state, N, g0 + lane);
     const int v = (views && valid) ? views[g0 + lane] : view;
-    emit_views<G>(stage[warp], s, valid, v, g0, ng, lane, out_main, out_scalar, out_amask, out_bits);
+    emit_views<G>(stage, warp, s, valid, v, g0, ng, lane, out_main, out_scalar, out_amask, out_bits);
 }
 
 // Fused ply: apply the chosen actions, report reward / terminal / outcome, optionally
@@ -144,7 +163,8 @@ __global__ void __launch_bounds__(BLK)
 k_step_observe(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, const int32_t* __restrict__ sel,
                int auto_reset, float* out_main, float* out_scalar, float* out_amask, float* __restrict__ out_reward,
                uint8_t* __restrict__ out_terminal, float* __restrict__ out_outcome, int32_t* __restrict__ out_turn) {
-    __shared__ WarpStage<G> stage[WARPS];
+    __shared__ CtaStage<G> stage;
+    stage.init();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t g0 = (blockIdx.x * (int64_t)WARPS + warp) * 32;
     if (g0 >= N) return;
@@ -174,7 +194,7 @@ k_step_observe(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, 
         if (a >= 0 || (term && auto_reset)) G::store(state, N, i, s);
         if (out_turn) out_turn[i] = G::turn(s);
     }
-    emit_views<G>(stage[warp], s, valid, B200RL_VIEW_TURN, g0, ng, lane, out_main, out_scalar, out_amask, nullptr);
+    emit_views<G>(stage, warp, s, valid, B200RL_VIEW_TURN, g0, ng, lane, out_main, out_scalar, out_amask, nullptr);
 }
 
 // k-th (0-based) set bit of an LW-word mask
@@ -217,8 +237,9 @@ struct RolloutParams {
 // n_plies plies; every ply emits the reference-format moment data (observation,
 // action_mask, action) and/or a 32-byte compact trajectory record.
 template <class G>
-__global__ void __launch_bounds__(BLK) k_rollout(const RolloutParams p) {
-    __shared__ WarpStage<G> stage[WARPS];
+__global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
+    __shared__ CtaStage<G> stage;
+    stage.init();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t g0 = (blockIdx.x * (int64_t)WARPS + warp) * 32;
     if (g0 >= p.N) return;
@@ -253,7 +274,7 @@ __global__ void __launch_bounds__(BLK) k_rollout(const RolloutParams p) {
         }
         const int64_t wv = p.waves > 0 ? (int64_t)(it % (uint64_t)p.waves) : 0;
         if (p.out_main || p.out_amask || p.out_scalar) {
-            emit_views<G>(stage[warp], s, valid, B200RL_VIEW_TURN, g0, ng, lane,
+            emit_views<G>(stage, warp, s, valid, B200RL_VIEW_TURN, g0, ng, lane,
                           p.out_main ? p.out_main + wv * p.N * G::OBITS : nullptr,
                           p.out_scalar ? p.out_scalar + wv * p.N * G::SBITS : nullptr,
                           p.out_amask ? p.out_amask + wv * p.N * G::A : nullptr, nullptr);

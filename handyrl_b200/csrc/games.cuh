@@ -186,11 +186,21 @@ struct GeisterGame {
         o1 = s.win == 1 ? -1.f : (s.win == 2 ? 1.f : 0.f);
     }
 
+    // Plane / position-word selection without dynamic indexing (keeps State in registers).
+    __device__ __forceinline__ static uint64_t bbsel(const State& s, int k) {
+        const uint64_t lo = (k & 1) ? s.bb[1] : s.bb[0], hi = (k & 1) ? s.bb[3] : s.bb[2];
+        return (k & 2) ? hi : lo;
+    }
+    __device__ __forceinline__ static uint32_t possel(const State& s, int k) {
+        const uint32_t lo = (k & 1) ? s.pos[1] : s.pos[0], hi = (k & 1) ? s.pos[3] : s.pos[2];
+        return (k & 2) ? hi : lo;
+    }
+
     // piece_cnt[k] of the reference.  `spare` holds four signed byte corrections that are non-zero only
     // in network-match mirror environments, where update() rewrites a captured piece's type on the
     // board without touching piece_cnt (geister.py:416-424).
     __device__ __forceinline__ static int cnt(const State& s, int k) {
-        return __popcll(s.bb[k]) + (int)(int8_t)((s.spare >> (8 * k)) & 0xFF);
+        return __popcll(bbsel(s, k)) + (int)(int8_t)((s.spare >> (8 * k)) & 0xFF);
     }
 
     __device__ __forceinline__ static void pos_replace(State& s, uint32_t cell, uint32_t newv) {
@@ -218,10 +228,11 @@ struct GeisterGame {
                 if ((blue >> k) & 1) bbl |= 1ull << cell; else bbr |= 1ull << cell;
                 if (k < 4) p0 |= cell << (8 * k); else p1 |= cell << (8 * (k - 4));
             }
-            s.bb[c * 2] |= bbl;
-            s.bb[c * 2 + 1] |= bbr;
-            s.pos[c * 2] = p0;
-            s.pos[c * 2 + 1] = p1;
+            if (c == 0) {
+                s.bb[0] |= bbl; s.bb[1] |= bbr; s.pos[0] = p0; s.pos[1] = p1;
+            } else {
+                s.bb[2] |= bbl; s.bb[3] |= bbr; s.pos[2] = p0; s.pos[3] = p1;
+            }
             s.aux = (s.aux & ~(0xFFu << (8 + 8 * c))) | ((uint32_t)(layout + 1) << (8 + 8 * c));
             s.tc += 1;
             return;
@@ -240,7 +251,8 @@ struct GeisterGame {
         if (piece < 0) return;  // no piece on the from-cell: not a legal action, ignored
         uint32_t captured = 0;
         if (!onboard) {  // finish by goal (geister.py:370-373)
-            s.bb[piece] &= ~fbit;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s.bb[k] &= ~fbit;  // only plane `piece` holds the bit
             pos_replace(s, from, 0xFF);
             s.win = c + 1;
         } else {
@@ -251,12 +263,14 @@ struct GeisterGame {
             for (int k = 0; k < 4; ++k)
                 if (s.bb[k] & tbit) cap = k;
             if (cap >= 0) {  // geister.py:376-385
-                s.bb[cap] &= ~tbit;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) s.bb[k] &= ~tbit;  // only plane `cap` holds the bit
                 pos_replace(s, to, 0xFF);
                 if (cnt(s, cap) == 0) s.win = ((cap & 1) == 0) ? (c + 1) : (2 - c);
                 captured = (cap & 1) + 1;
             }
-            s.bb[piece] = (s.bb[piece] & ~fbit) | tbit;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s.bb[k] = (s.bb[k] & ~fbit) | (k == piece ? tbit : 0ull);
             pos_replace(s, from, to);
         }
         s.aux = (s.aux & ~3u) | captured;
@@ -267,13 +281,13 @@ struct GeisterGame {
     // From-cell sets per ABSOLUTE direction d (geister.py:447-470).
     __device__ __forceinline__ static void from_sets(const State& s, uint64_t (&F)[4]) {
         const int c = s.tc & 1;
-        const uint64_t own = s.bb[c * 2] | s.bb[c * 2 + 1];
+        const uint64_t own = c ? (s.bb[2] | s.bb[3]) : (s.bb[0] | s.bb[1]);
         const uint64_t fre = ~own & G_M36;
         F[0] = own & (fre << 6) & G_M36;
         F[1] = own & (fre << 1) & ~G_COL_Y0 & G_M36;
         F[2] = own & (fre >> 1) & ~G_COL_Y5;
         F[3] = own & (fre >> 6);
-        const uint64_t blue = s.bb[c * 2];
+        const uint64_t blue = c ? s.bb[2] : s.bb[0];
         // goal exits: BLACK leaves sideways from (0,5)/(5,5), WHITE from (0,0)/(5,0) (geister.py:183-186)
         if (c == 0) {
             F[0] |= blue & (1ull << 5);
@@ -317,7 +331,7 @@ struct GeisterGame {
         from_sets(s, F);
         const int c = s.tc & 1;
         for (int k = 0; k < 8; ++k) {
-            const uint32_t p = (s.pos[c * 2 + (k >> 2)] >> (8 * (k & 3))) & 0xFF;
+            const uint32_t p = (possel(s, c * 2 + (k >> 2)) >> (8 * (k & 3))) & 0xFF;
             if (p == 0xFF) continue;
             for (int d = 0; d < 4; ++d)
                 if ((F[d] >> p) & 1) out[n++] = c ? ((3 - d) * 36 + 35 - (int)p) : (d * 36 + (int)p);
@@ -349,7 +363,8 @@ struct GeisterGame {
         const bool turn_view = (view == B200RL_VIEW_NONE) || (view == B200RL_VIEW_TURN) || (view == tp);
         const int vc = turn_view ? tp : 1 - tp;
         const int oc = 1 - vc;
-        const uint64_t cb = s.bb[vc * 2], cr = s.bb[vc * 2 + 1], obl = s.bb[oc * 2], ore = s.bb[oc * 2 + 1];
+        const uint64_t cb = vc ? s.bb[2] : s.bb[0], cr = vc ? s.bb[3] : s.bb[1];
+        const uint64_t obl = vc ? s.bb[0] : s.bb[2], ore = vc ? s.bb[1] : s.bb[3];
         scalar = (vc == 0 ? 1u : 0u) | (turn_view ? 2u : 0u) | (onehot4(cnt(s, vc * 2)) << 2) |
                  (onehot4(cnt(s, vc * 2 + 1)) << 6) | (onehot4(cnt(s, oc * 2)) << 10) |
                  (onehot4(cnt(s, oc * 2 + 1)) << 14);

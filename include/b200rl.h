@@ -203,6 +203,18 @@ int b200rl_make_batch(int game, const void* traj, int64_t D, int64_t N, const fl
                       float* tmask, float* omask, float* progress, void* stream);
 
 /*
+ * Batcher.select_episode (handyrl/train.py:284-302) for B windows: recency-biased rejection sampling
+ * over the last min(finished, E, maximum_episodes) rows of the finished-episode table (index 0 =
+ * oldest), then a uniform window start.  Rows whose first ply left the trajectory ring (older than D
+ * iterations before it_now) are rejected.  Draws: counter RNG keyed (seed, b, draw0 + 4*try + j).
+ *   out_windows (B,8) int32 in the layout b200rl_make_batch consumes (solo player = 1 random bit).
+ * Reads counters[5] on the device: no host synchronisation between rollout and window selection.
+ */
+int b200rl_select_windows(const int32_t* ep_table, int64_t E, const uint64_t* counters, int64_t maximum_episodes,
+                          int64_t forward_steps, uint64_t seed, uint64_t draw0, uint64_t it_now, int64_t D,
+                          int32_t* out_windows, int64_t B, void* stream);
+
+/*
  * Padding + stacking step of make_batch (train.py:92-122) for episodes that were decoded on the
  * host (reference wire format): `src` holds the windows of all B episodes back to back, rows of
  * `row_words` 32-bit words, episode b owning rows offsets[b]..offsets[b+1]; out is (B, T, row)
