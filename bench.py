@@ -3,19 +3,24 @@
 
 Workload (BASELINE.json configs[1]): Geister self-play, 65,536 concurrent games per GPU,
 epoch-0 policy (uniform over legal actions == RandomModel), V-Trace policy + UPGO value
-targets.  One *step* is one pass of the hot path over one batch of synthetic input:
+targets.  One *step* is one pass of the whole hot path over one batch of synthetic input:
 
-  1. rollout   : PLIES plies for all 65,536 games in one persistent launch; every ply
-                 writes the reference-format moment (observation 7x6x6 + 18, action_mask
-                 214 fp32, action) plus a 32-byte trajectory record          -> env-steps
-  2. make_batch: B windows of T plies gathered from the device trajectory ring into the
-                 (B,T,P,...) training batch (when the kernel is available)
-  3. targets   : compute_target pair (UPGO value targets + V-Trace policy advantages) for
-                 the value head and the return head on (B,T,2,1)              -> target timesteps
+  1. rollout     : PLIES plies for all 65,536 games in one persistent launch; every ply writes the
+                   reference-format moment (observation 7x6x6 + 18, action_mask 214 fp32, action)
+                   plus a 32-byte trajectory record                              -> env-steps
+  2. select      : B training windows drawn on the device from the finished-episode table
+                   (Batcher.select_episode, train.py:284-302)
+  3. make_batch  : the B windows x T plies re-encoded from the trajectory ring into the
+                   reference's 12-tensor (B,T,P,...) batch (train.py:33-133)      -> batch timesteps
+  4. targets     : compute_target pair (UPGO value targets + V-Trace policy advantages) for the
+                   value head (bootstrap = batch outcome) and the return head (batch return /
+                   reward) on (B,T,2,1)                                          -> target timesteps
 
-`value` = env-steps/s of the whole job (all ranks) over the wall time of the K timed steps
-(device time, max over ranks).  Inputs are device resident; `e2e` repeats the stepping
-through host buffers (pinned H2D actions, D2H observation/mask/reward/terminal).
+`value` = env-steps/s of the whole job (all ranks) over the device time of the K timed steps (max
+over ranks); every generated ply is batched and targeted once (B*T == games*plies).  Inputs are
+device resident.  `e2e` runs the same step through the public API with the replay index on the
+HOST: finished-episode rows are read back, windows are selected with numpy and uploaded from pinned
+memory, and a scalar summary of the targets is read back every step.
 
   python bench.py --gpus N --steps K --warmup W          # N>1 under torchrun
   python bench.py --impl reference ...                   # CPU oracle port on the host cores
@@ -26,7 +31,6 @@ import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -35,16 +39,22 @@ sys.path.insert(0, ROOT)
 N_GAMES = 65536
 PLIES = 32
 B, T, P = 65536, 32, 2
-BYTES_PER_ENV_STEP = 1940          # obs 1008 + scalar 72 + action_mask 856 + action 4
-BYTES_PER_TARGET_ELEM = 20         # fused V-Trace + UPGO pass: v, r, rho/2, c/2 in; target, adv out
+RING_DEPTH = 512
+TRAIN_ARGS = {"turn_based_training": True, "observation": False, "gamma": 0.8, "forward_steps": T,
+              "compress_steps": 4, "maximum_episodes": 100000, "lambda": 0.7,
+              "policy_target": "VTRACE", "value_target": "UPGO"}
+# Algorithmic HBM bytes per unit
+BYTES_PER_ENV_STEP = 1940 + 32     # obs 1008 + scalar 72 + action_mask 856 + action 4, + 32 B trajectory record
+BYTES_PER_BATCH_CELL = 2848 + 32   # the 12 batch tensors of one (b,t) in TURN mode, + the 32 B record read
+BYTES_PER_TARGET_PAIR = 16 + 20    # value head (v, rho/2, c/2 in; 2 out) + return head (+ rewards), per (b,t,p)
 
 
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         with open(p) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured"
-    return 6650.0, "fallback"
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler:
@@ -64,7 +74,8 @@ class ClockSampler:
             os.close(fd)
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+                 "-lms", "20"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+            time.sleep(0.3)  # let the first samples land before the timed region starts
         except Exception:
             self.proc = None
 
@@ -72,7 +83,7 @@ class ClockSampler:
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if self.proc is None:
             return out
-        time.sleep(0.15)
+        time.sleep(0.1)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -102,22 +113,41 @@ class ClockSampler:
         return out
 
 
-def cpu_baseline(seconds_target=12.0):
-    """The C oracle's self-play loop (oracle/games_oracle.c: orc_selfplay) on all host cores."""
+def workload_config(n_gpus):
+    return {"workload": "Geister self-play hot path per step: %d concurrent games/GPU x %d plies (uniform epoch-0 "
+                        "policy, auto-reset, full fp32 moment per ply) -> device select_episode -> make_batch "
+                        "(B=%d,T=%d, turn-based) -> UPGO value targets + V-Trace policy advantages for the value and "
+                        "return heads on (B,T,%d,1)" % (N_GAMES, PLIES, B, T, P),
+            "games_per_gpu": N_GAMES, "plies_per_step": PLIES, "batch_shape": [B, T, P],
+            "value_target": "UPGO", "policy_target": "VTRACE", "lambda": 0.7, "gamma": 0.8,
+            "l2_policy": "inputs larger than L2: each step streams 4.1 GB of moments, 6.0 GB of batch tensors and "
+                         "rotates 8 sets of synthetic net outputs (4 x 16.8 MB each) against the 126 MB L2",
+            "parallelism": "games, windows and target rows sharded per GPU, no data-path collective (dp%d)" % n_gpus}
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the C oracle port on the host cores
+# ---------------------------------------------------------------------------------------------
+def cpu_hotpath(seconds_target, seed):
+    """One bounded sample of the hot path on all host cores through the oracle port (oracle/)."""
     from oracle import games_c
     cores = os.cpu_count() or 1
-    # calibrate, then run a bounded sample
     t0 = time.perf_counter()
-    n = games_c.selfplay("geister", 20000, seed=1, n_threads=cores)
-    dt = time.perf_counter() - t0
-    rate = n / dt
+    n = games_c.selfplay("geister", 20000, seed=seed, n_threads=cores)
+    rate = n / (time.perf_counter() - t0)
     per_thread = max(20000, int(rate * seconds_target / cores))
     t0 = time.perf_counter()
-    n = games_c.selfplay("geister", per_thread, seed=2, n_threads=cores)
+    n = games_c.selfplay("geister", per_thread, seed=seed + 1, n_threads=cores)
     dt = time.perf_counter() - t0
+    return n, dt, cores, per_thread
+
+
+def cpu_baseline(seconds_target=12.0):
+    n, dt, cores, per_thread = cpu_hotpath(seconds_target, 1)
     return {"value": n / dt, "unit": "env-steps/s", "cores": cores, "kind": "port",
-            "sample": "%d Geister env-steps (obs + action_mask + policy + uniform action + play) per thread x %d "
-                      "pthreads of the C oracle, %.1f s" % (per_thread, cores, dt)}
+            "sample": "%d Geister env-steps per thread x %d pthreads of the C oracle (obs + action_mask + policy + "
+                      "uniform action + play per ply; batch assembly and targets not included), %.1f s"
+                      % (per_thread, cores, dt)}
 
 
 def run_reference(args, rank, world):
@@ -139,10 +169,12 @@ def run_reference(args, rank, world):
     line = {
         "impl": "reference", "metric": "geister_selfplay_env_steps_per_sec", "value": v, "unit": "env-steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64 bitboards -> f32",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32 cell arrays -> f32",
         "data": "synthetic", "config": workload_config(args.gpus),
         "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                         "sample": "%d env-steps per thread x %d pthreads per step (C oracle orc_selfplay)"
+                         "sample": "%d env-steps per thread x %d pthreads per step (C oracle orc_selfplay: obs + "
+                                   "action_mask + policy + uniform action + play per ply; the batch-assembly and "
+                                   "target phases of the GPU arm's step are NOT run here, which favours this arm)"
                                    % (per_thread, cores)},
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -150,17 +182,7 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(n_gpus):
-    return {"workload": "Geister self-play, %d concurrent games/GPU x %d plies per step (uniform epoch-0 policy, "
-                        "auto-reset), full moment output per ply; then V-Trace policy + UPGO value targets on "
-                        "(B=%d,T=%d,P=%d) for value and return heads" % (N_GAMES, PLIES, B, T, P),
-            "games_per_gpu": N_GAMES, "plies_per_step": PLIES, "target_shape": [B, T, P],
-            "value_target": "UPGO", "policy_target": "VTRACE", "lambda": 0.7, "gamma": 0.8,
-            "l2_policy": "inputs larger than L2: 2 waves x 127 MB of moment output, 4 x 16.8 MB target inputs "
-                         "rotated over 8 buffer sets",
-            "parallelism": "games sharded per GPU, no data-path collective (dp%d)" % n_gpus}
-
-
+# ---------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -180,10 +202,12 @@ def main():
         run_reference(args, rank, world)
         return
 
+    import numpy as np
     import torch
     import torch.distributed as dist
-    from handyrl_b200.engine import BatchedEnv
+    from handyrl_b200.generation import BatchGenerator
     from handyrl_b200.losses import compute_target_pair
+    from handyrl_b200.train import make_batch_windows, select_windows_host
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -191,55 +215,60 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     # ---------------- device-resident workload ----------------
-    env = BatchedEnv("Geister", N_GAMES, device=dev)
+    gen = BatchGenerator("Geister", N_GAMES, device=dev, seed=1234, game_id_base=rank * N_GAMES, depth=RING_DEPTH,
+                         max_episodes=1 << 20, args={})
+    env = gen.env
     WAVES = 2
     main_w, scalar_w = env.alloc_obs(waves=WAVES)
     waves = dict(main=main_w, scalar=scalar_w, action_mask=torch.empty(WAVES, N_GAMES, env.A, device=dev))
     act_w = torch.empty(WAVES, N_GAMES, dtype=torch.int32, device=dev)
-    D = 512
-    traj = torch.zeros(D, 2, N_GAMES, 4, dtype=torch.int32, device=dev)
-    ept = torch.zeros(1 << 20, 4, dtype=torch.int32, device=dev)
-    ctr = torch.zeros(8, dtype=torch.int64, device=dev)
+    windows = torch.empty(B, 8, dtype=torch.int32, device=dev)
 
     g = torch.Generator(device=dev).manual_seed(rank)
-    NSETS = 8  # rotate input sets so that consecutive steps do not hit L2 (8 x 4 x 16.8 MB > 126 MB)
+    NSETS = 8  # rotate the synthetic net outputs so that consecutive steps do not hit L2
     tsets = []
     for _ in range(NSETS):
-        v = torch.tanh(torch.randn(B, T, P, 1, device=dev, generator=g))
-        rho = torch.exp(0.5 * torch.randn(B, T, 1, 1, device=dev, generator=g)).clamp(0, 1)
-        oc = torch.randint(-1, 2, (B, 1, P, 1), device=dev, generator=g).float()
-        rew = torch.full((B, T, P, 1), -0.01, device=dev)
-        ret = torch.randn(B, T, P, 1, device=dev, generator=g)
-        vr = torch.tanh(torch.randn(B, T, P, 1, device=dev, generator=g))
-        tsets.append((v, oc, rho, vr, ret, rew))
+        v = torch.tanh(torch.randn(B, T, P, 1, device=dev, generator=g))        # value head output
+        vr = torch.tanh(torch.randn(B, T, P, 1, device=dev, generator=g))       # return head output
+        rho = torch.exp(0.5 * torch.randn(B, T, 1, 1, device=dev, generator=g)).clamp(0, 1)   # train.py:230
+        c = rho.clone()                                                          # train.py:231
+        tsets.append((v, vr, rho, c))
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
+    state = {"batch": None}
 
-    def step(k, evs=None):
-        if evs:
-            evs[0].record()
-        env.rollout(PLIES, seed=1234, game_id_base=rank * N_GAMES, waves=waves, traj=traj, ep_table=ept,
-                    counters=ctr, out_action=act_w)
-        if evs:
-            evs[1].record()
-        v, oc, rho, vr, ret, rew = tsets[k % NSETS]
-        compute_target_pair("UPGO", "VTRACE", v, oc, None, 0.7, 1.0, rho, rho)
-        compute_target_pair("UPGO", "VTRACE", vr, ret, rew, 0.7, 0.8, rho, rho)
-        if evs:
-            evs[2].record()
+    def step(k, evs=None, win=None):
+        rec = (lambda i: evs[i].record()) if evs else (lambda i: None)
+        rec(0)
+        gen.rollout(PLIES, waves=waves, out_action=act_w)
+        rec(1)
+        if win is None:
+            gen.select_windows(B, TRAIN_ARGS, out=windows)
+            win = windows
+        state["batch"] = batch = make_batch_windows(gen.store, win, TRAIN_ARGS, out=state["batch"])
+        rec(2)
+        v, vr, rho, c = tsets[k % NSETS]
+        # train.py:245-253 with value_target UPGO / policy_target VTRACE: targets of the first, advantages of the second
+        t1 = compute_target_pair("UPGO", "VTRACE", v, batch["outcome"], None, 0.7, 1.0, rho, c)
+        t2 = compute_target_pair("UPGO", "VTRACE", vr, batch["return"], batch["reward"], 0.7, 0.8, rho, c)
+        rec(3)
+        return t1, t2
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    # fill the finished-episode table before anything is timed (Geister games last ~157 plies)
+    for _ in range(8):
+        gen.rollout(PLIES, waves=waves, out_action=act_w)
     for k in range(args.warmup):
         step(k)
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    phase_evs = [[ev(), ev(), ev()] for _ in range(args.steps)]
+    phase_evs = [[ev() for _ in range(4)] for _ in range(args.steps)]
     e0, e1 = ev(), ev()
     barrier()
     e0.record()
@@ -249,82 +278,151 @@ def main():
     barrier()
     total_ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
-    roll_ms = sum(p[0].elapsed_time(p[1]) for p in phase_evs) / args.steps
-    tgt_ms = sum(p[1].elapsed_time(p[2]) for p in phase_evs) / args.steps
+    ph = [sum(p[i].elapsed_time(p[i + 1]) for p in phase_evs) / args.steps for i in range(3)]
     if world > 1:
-        tt = torch.tensor([total_ms, roll_ms, tgt_ms], device=dev, dtype=torch.float64)
+        tt = torch.tensor([total_ms] + ph, device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        total_ms, roll_ms, tgt_ms = [float(x) for x in tt.tolist()]
+        total_ms, ph = float(tt[0]), [float(x) for x in tt[1:]]
+    roll_ms, batch_ms, tgt_ms = ph
 
     env_steps_per_step = N_GAMES * PLIES * world
     value = env_steps_per_step * args.steps / (total_ms * 1e-3)
-    tgt_elems = 2 * B * T * P * world
 
-    # ---------------- e2e: host buffers through the public API ----------------
+    # ---------------- e2e: the same step through the public API with the replay index on the host ----------
     e2e = None
     if not args.no_e2e:
-        e2e_env = BatchedEnv("Geister", N_GAMES, device=dev)
-        out = e2e_env.step_observe(None)
-        h_act = torch.zeros(N_GAMES, dtype=torch.int32).pin_memory()
-        h = {k: torch.empty(t.shape, dtype=t.dtype).pin_memory() for k, t in out.items() if t is not None}
-        d_act = torch.empty(N_GAMES, dtype=torch.int32, device=dev)
-        E2E_PLIES = 8
+        cap = TRAIN_ARGS["maximum_episodes"]
+        mirror = np.zeros((0, 4), dtype=np.int32)
+        rows_pin = torch.empty(1 << 16, 4, dtype=torch.int32).pin_memory()
+        win_pin = torch.empty(B, 8, dtype=torch.int32).pin_memory()
+        win_dev = torch.empty(B, 8, dtype=torch.int32, device=dev)
+        met_pin = torch.empty(4, dtype=torch.float32).pin_memory()
+        rng = np.random.default_rng(rank)
+        gen.finished_rows()  # drop what the device-resident run produced; the host index starts here
+        d2h_bytes = []
 
-        def e2e_step():
-            nonlocal out
-            for _ in range(E2E_PLIES):
-                # host policy on the host copy of the mask: first legal action (argmin of the 0 / 1e32 mask)
-                torch.argmin(h["action_mask"], dim=1, out=h_idx)
-                h_act.copy_(h_idx)
-                d_act.copy_(h_act, non_blocking=True)                      # H2D: this ply's actions
-                out = e2e_env.step_observe(d_act, auto_reset=True, out=out)
-                for k2, t in h.items():                                     # D2H: obs, mask, reward, terminal ...
-                    t.copy_(out[k2], non_blocking=True)
-                torch.cuda.current_stream().synchronize()
+        def e2e_step(k):
+            nonlocal mirror
+            gen.rollout(PLIES, waves=waves, out_action=act_w)
+            rows = gen.finished_rows(rows_pin)                                  # D2H: new finished-episode rows
+            mirror = np.concatenate([mirror, rows])[-cap:]
+            win = select_windows_host(mirror, B, TRAIN_ARGS, rng, it_now=gen.store.it, depth=gen.store.D)
+            win_pin.copy_(torch.from_numpy(win))
+            win_dev.copy_(win_pin, non_blocking=True)                           # H2D: this step's windows
+            (tv, av), (tr, ar) = step_tail(k, win_dev)
+            met = torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()])
+            met_pin.copy_(met, non_blocking=True)                               # D2H: the step's result
+            torch.cuda.current_stream().synchronize()
+            d2h_bytes.append(rows.nbytes + 8 + met_pin.numel() * 4)
+            return float(met_pin[0])
 
-        h_idx = torch.zeros(N_GAMES, dtype=torch.int64)
-        for k2, t in h.items():
-            t.copy_(out[k2])
-        torch.set_num_threads(max(1, (os.cpu_count() or 1) // max(world, 1)))
-        for _ in range(2):
-            e2e_step()
+        def step_tail(k, win):
+            state["batch"] = batch = make_batch_windows(gen.store, win, TRAIN_ARGS, out=state["batch"])
+            v, vr, rho, c = tsets[k % NSETS]
+            t1 = compute_target_pair("UPGO", "VTRACE", v, batch["outcome"], None, 0.7, 1.0, rho, c)
+            t2 = compute_target_pair("UPGO", "VTRACE", vr, batch["return"], batch["reward"], 0.7, 0.8, rho, c)
+            return t1, t2
+
+        for k in range(3):
+            e2e_step(k)
         barrier()
-        ksteps = max(2, min(args.steps, 5))
+        ksteps = max(3, min(args.steps, 10))
+        d2h_bytes.clear()
         t0 = time.perf_counter()
-        for _ in range(ksteps):
-            e2e_step()
+        for k in range(ksteps):
+            e2e_step(k)
         barrier()
         dt = time.perf_counter() - t0
         if world > 1:
             tt = torch.tensor([dt], device=dev, dtype=torch.float64)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt.item())
-        d2h = sum(t.numel() * t.element_size() for t in h.values())
-        e2e = {"value": N_GAMES * E2E_PLIES * ksteps * world / dt, "unit": "env-steps/s",
-               "h2d_bytes_per_step": int(h_act.numel() * 4 * E2E_PLIES), "d2h_bytes_per_step": int(d2h * E2E_PLIES),
-               "plies_per_step": E2E_PLIES,
-               "note": "BatchedEnv.step_observe per ply with pinned-host actions in and observation/action_mask/"
-                       "reward/terminal/outcome/turn out; PCIe-bound"}
+        e2e = {"value": N_GAMES * PLIES * ksteps * world / dt, "unit": "env-steps/s",
+               "h2d_bytes_per_step": int(win_pin.numel() * 4), "d2h_bytes_per_step": int(sum(d2h_bytes) / len(d2h_bytes)),
+               "steps": ksteps, "ms_per_step": dt / ksteps * 1e3,
+               "note": "BatchGenerator.rollout -> finished_rows (D2H) -> select_windows_host (numpy, host replay index) "
+                       "-> pinned H2D windows -> make_batch_windows -> compute_target_pair x2 -> D2H target summary; "
+                       "moments stay in HBM (the trajectory ring is the replay buffer), wall clock incl. host work"}
+
+        # the same self-play driven ply by ply from HOST buffers (reference Environment-style stepping: actions
+        # H2D, observation / legal bits / reward / terminal D2H every ply) — PCIe-bound by the fp32 observations
+        from handyrl_b200.engine import BatchedEnv
+        henv = BatchedEnv("Geister", N_GAMES, device=dev)
+        out = henv.step_observe(None)
+        keys = ("main", "scalar", "action_mask", "reward", "terminal")
+        h = {k2: torch.empty(out[k2].shape, dtype=out[k2].dtype).pin_memory() for k2 in keys}
+        h_act = torch.zeros(N_GAMES, dtype=torch.int32).pin_memory()
+        h_idx = torch.zeros(N_GAMES, dtype=torch.int64)
+        d_act = torch.empty(N_GAMES, dtype=torch.int32, device=dev)
+        for k2 in keys:
+            h[k2].copy_(out[k2])
+        torch.set_num_threads(max(1, (os.cpu_count() or 1) // max(world, 1)))
+
+        def host_ply():
+            nonlocal out
+            torch.argmin(h["action_mask"], dim=1, out=h_idx)                # host policy: first legal action
+            h_act.copy_(h_idx)
+            d_act.copy_(h_act, non_blocking=True)                           # H2D
+            out = henv.step_observe(d_act, auto_reset=True, out=out)
+            for k2 in keys:
+                h[k2].copy_(out[k2], non_blocking=True)                     # D2H
+            torch.cuda.current_stream().synchronize()
+
+        for _ in range(4):
+            host_ply()
+        barrier()
+        nply = 16
+        t0 = time.perf_counter()
+        for _ in range(nply):
+            host_ply()
+        barrier()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            tt = torch.tensor([dt], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = float(tt.item())
+        d2h = sum(t_.numel() * t_.element_size() for t_ in h.values())
+        e2e["host_stepping"] = {"value": N_GAMES * nply * world / dt, "unit": "env-steps/s",
+                                "h2d_bytes_per_ply": int(h_act.numel() * 4), "d2h_bytes_per_ply": int(d2h),
+                                "pcie_gbs": d2h * nply / dt / 1e9,
+                                "note": "BatchedEnv.step_observe per ply with pinned-host actions in and fp32 "
+                                        "observation/action_mask/reward/terminal out (1.96 kB per env-step over PCIe)"}
 
     if rank == 0:
         peak, peak_kind = load_peaks()
-        achieved = BYTES_PER_ENV_STEP * N_GAMES * PLIES / (roll_ms * 1e-3) / 1e9
-        t_ach = BYTES_PER_TARGET_ELEM * (tgt_elems / world) / (tgt_ms * 1e-3) / 1e9
+
+        def roof(kernel, nbytes, ms, unit_bytes, unit_name):
+            a = nbytes / (ms * 1e-3) / 1e9
+            return {"kernel": kernel, "bound": "hbm", "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak,
+                    "traffic": None, "peak_kind": peak_kind, "bytes_per_unit": unit_bytes, "unit_name": unit_name,
+                    "avg_ms": ms}
+
+        roofs = {
+            "rollout": roof("k_rollout<Geister>", BYTES_PER_ENV_STEP * N_GAMES * PLIES, roll_ms, BYTES_PER_ENV_STEP,
+                            "env-step"),
+            "make_batch": roof("k_select_windows + k_make_batch<Geister>", BYTES_PER_BATCH_CELL * B * T, batch_ms,
+                               BYTES_PER_BATCH_CELL, "(b,t) batch cell"),
+            "targets": roof("k_target_scan<UPGO,VTRACE> x2 (value + return head)", BYTES_PER_TARGET_PAIR * B * T * P,
+                            tgt_ms, BYTES_PER_TARGET_PAIR, "(b,t,p) element, both heads"),
+        }
+        dominant = max(roofs, key=lambda k: roofs[k]["avg_ms"])
+        traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(traffic_file):
+            with open(traffic_file) as f:
+                tr = json.load(f)
+            for k in roofs:
+                roofs[k]["traffic"] = tr.get(k)
         line = {
             "metric": "geister_selfplay_env_steps_per_sec", "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64 bitboards -> f32", "data": "synthetic", "config": workload_config(world),
-            "target_timesteps_per_sec": tgt_elems / (tgt_ms * 1e-3),
-            "phases": {"rollout_ms": roll_ms, "targets_ms": tgt_ms,
+            "target_timesteps_per_sec": B * T * P * world / (tgt_ms * 1e-3),
+            "batch_timesteps_per_sec": B * T * world / (batch_ms * 1e-3),
+            "phases": {"rollout_ms": roll_ms, "make_batch_ms": batch_ms, "targets_ms": tgt_ms,
                        "env_steps_per_sec_rollout_only": env_steps_per_step / (roll_ms * 1e-3)},
-            "roofline": {"kernel": "k_rollout<Geister>", "bound": "hbm", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
-                         "bytes_per_unit": BYTES_PER_ENV_STEP},
-            "roofline_targets": {"kernel": "k_target_scan<UPGO,VTRACE>", "bound": "hbm", "achieved": t_ach,
-                                 "peak": peak, "unit": "GB/s", "frac": t_ach / peak,
-                                 "bytes_per_unit": BYTES_PER_TARGET_ELEM},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": 3 * args.steps,
+            "roofline": roofs[dominant], "rooflines": roofs,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": 5 * args.steps,
         }
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline()

@@ -292,7 +292,8 @@ k_select_windows(const int32_t* __restrict__ ep_table, int64_t E, const unsigned
     const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (b >= B) return;
     const unsigned long long cursor = counters[5];
-    int64_t L = (int64_t)min(cursor, (unsigned long long)E);
+    // the reference trims self.episodes to maximum_episodes (train.py:502-503)
+    const int64_t L = min((int64_t)min(cursor, (unsigned long long)E), maximum_episodes);
     int32_t* w = out + b * 8;
     if (L <= 0) {  // nothing finished yet: an empty window (all rows padded)
         w[0] = 0; w[1] = 0; w[2] = 0; w[3] = 0; w[4] = 0; w[5] = 1; w[6] = 3; w[7] = 0;

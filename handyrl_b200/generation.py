@@ -98,11 +98,49 @@ class BatchGenerator:
         env.it = st.it
         return term
 
+    # -- window selection on the device (Batcher.select_episode, train.py:284-302) -------
+    def select_windows(self, batch_size, args, seed=None, out=None):
+        """(batch_size, 8) int32 windows for `train.make_batch_windows`, drawn on the device from the
+        finished-episode table without a host round trip."""
+        st, env = self.store, self.env
+        if out is None:
+            out = torch.empty(batch_size, 8, dtype=torch.int32, device=env.device)
+        self._draws = getattr(self, "_draws", 0)
+        with torch.cuda.device(env.device):
+            _lib.call("b200rl_select_windows", _ptr(st.ep_table), st.E, _ptr(st.counters),
+                      int(args['maximum_episodes']), int(args['forward_steps']),
+                      int(self.seed if seed is None else seed) ^ 0x5E1EC7, self._draws, st.it, st.D, _ptr(out),
+                      int(batch_size), env._stream())
+        self._draws += 256
+        return out
+
     # -- finished episodes ------------------------------------------------------------
     def stats(self):
         c = self.store.counters.cpu().numpy()
         return {"episodes": int(c[0]), "env_steps": int(c[1]), "wins0": int(c[2]), "wins1": int(c[3]),
                 "draws": int(c[4])}
+
+    def finished_rows(self, out_host=None):
+        """Rows of the finished-episode table added since the last call (device -> host), oldest first:
+        (n,4) int32 {slot, steps | win << 16, end_it lo, end_it hi}.  This is what a host-side replay index
+        needs (the moments themselves stay in the trajectory ring)."""
+        st = self.store
+        cur = int(st.counters[5].item())
+        lo = max(st._ep_read, cur - st.E)
+        st._ep_read = cur
+        if cur <= lo:
+            return np.zeros((0, 4), dtype=np.int32)
+        a, b = lo % st.E, cur % st.E
+        if a < b:
+            rows = st.ep_table[a:b]
+        else:
+            rows = torch.cat([st.ep_table[a:], st.ep_table[:b]])
+        if out_host is not None and out_host.shape[0] >= rows.shape[0]:
+            h = out_host[:rows.shape[0]]
+            h.copy_(rows, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return h.numpy()
+        return rows.cpu().numpy()
 
     def episodes(self):
         """Episodes finished since the last call, in reference form

@@ -25,6 +25,7 @@ from .engine import _ptr
 from .generation import DeviceMoments
 
 _RET_CACHE = {}
+_RET_DEV_CACHE = {}
 
 
 def _return_table(gamma, reward, n):
@@ -38,6 +39,13 @@ def _return_table(gamma, reward, n):
             tab.append(ret)
         _RET_CACHE[key] = np.asarray(tab, dtype=np.float32)
     return _RET_CACHE[key]
+
+
+def _return_table_dev(gamma, reward, n, dev):
+    key = (float(gamma), reward, n, str(dev))
+    if key not in _RET_DEV_CACHE:
+        _RET_DEV_CACHE[key] = torch.from_numpy(_return_table(gamma, reward, n)).to(dev)
+    return _RET_DEV_CACHE[key]
 
 
 def select_episode(episodes, args, rng=random):
@@ -63,6 +71,38 @@ def select_episode(episodes, args, rng=random):
     return ep_minimum
 
 
+def select_windows_host(ep_rows, batch_size, args, rng, it_now=None, depth=None):
+    """`select_episode` (handyrl/train.py:284-302) for a whole batch on the host, vectorised: `ep_rows` is the
+    host mirror of the finished-episode table, (L,4) int32 rows {slot, steps | win << 16, end_it lo, hi},
+    oldest first; `rng` a numpy Generator.  Returns the (batch_size, 8) int32 window rows that
+    `make_batch_windows` consumes (upload them from pinned memory)."""
+    L = len(ep_rows)
+    if L == 0:
+        raise _lib.B200RLError("select_windows_host: no finished episodes")
+    max_eps, T = int(args['maximum_episodes']), int(args['forward_steps'])
+    steps = (ep_rows[:, 1] & 0xFFFF).astype(np.int64)
+    end_it = ep_rows[:, 2].astype(np.uint32).astype(np.int64) | (ep_rows[:, 3].astype(np.uint32).astype(np.int64) << 32)
+    first_it = end_it + 1 - steps
+    alive = np.ones(L, dtype=bool) if it_now is None else (it_now - first_it <= depth)
+    idx = np.full(batch_size, -1, dtype=np.int64)
+    todo = np.arange(batch_size)
+    for _ in range(64):
+        if len(todo) == 0:
+            break
+        cand = rng.integers(0, min(L, max_eps), size=len(todo))                  # train.py:286
+        accept = 1 - (L - 1 - cand) / max_eps                                    # train.py:287
+        ok = (rng.random(len(todo)) < accept) & alive[cand]                      # train.py:288
+        idx[todo[ok]] = cand[ok]
+        todo = todo[~ok]
+    idx[todo] = L - 1   # like the device kernel: after 64 rejected draws take the newest episode
+    st = np.floor(rng.random(batch_size) * (1 + np.maximum(0, steps[idx] - T))).astype(np.int64)   # train.py:291-292
+    ed = np.minimum(st + T, steps[idx])                                          # train.py:293
+    first = first_it[idx] + st
+    win = np.stack([ep_rows[idx, 0].astype(np.int64), first & 0xFFFFFFFF, first >> 32, ed - st, st, steps[idx],
+                    (ep_rows[idx, 1].astype(np.int64) >> 16) & 3, rng.integers(0, 2, size=batch_size)], axis=1)
+    return (win & 0xFFFFFFFF).astype(np.uint32).view(np.int32)
+
+
 def _win_code(outcome):
     o0 = outcome[0]
     return 1 if o0 > 0 else (2 if o0 < 0 else 3)
@@ -72,15 +112,8 @@ def _make_batch_device(episodes, args):
     store = episodes[0]['moment'].store
     env = store.env
     dev = env.device
-    B, T = len(episodes), int(args['forward_steps'])
-    if args['turn_based_training'] and not args['observation']:
-        mode = 0
-    elif args['turn_based_training']:
-        mode = 1
-    else:
-        mode = 2
-    Po = 2 if mode == 1 else 1
-    Pv = 1 if mode == 2 else 2
+    B = len(episodes)
+    mode = batch_mode(args)
     win = np.zeros((B, 8), dtype=np.int64)
     for b, ep in enumerate(episodes):
         mo = ep['moment']
@@ -94,33 +127,51 @@ def _make_batch_device(episodes, args):
                   _win_code(ep['outcome']),
                   random.choice([0, 1]) if mode == 2 else 0)   # train.py:57-58
     wt = torch.from_numpy((win & 0xFFFFFFFF).astype(np.uint32).view(np.int32)).to(dev)
-    ret_tab = torch.from_numpy(_return_table(args['gamma'], -0.01 if env.has_reward else None,
-                                             env.max_steps + 1)).to(dev)
-    f32 = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
-    obs_main = f32(B, T, Po, *env.obs_shape)
-    obs_scalar = f32(B, T, Po, *env.scalar_shape) if env.scalar_shape else None
-    policy, amask = f32(B, T, Po, env.A), f32(B, T, Po, env.A)
-    action = torch.empty(B, T, Po, 1, dtype=torch.int64, device=dev)
-    value, reward, ret = f32(B, T, Pv, 1), f32(B, T, Pv, 1), f32(B, T, Pv, 1)
-    tmask, omask = f32(B, T, Pv, 1), f32(B, T, Pv, 1)
-    outcome, emask, progress = f32(B, 1, Pv, 1), f32(B, T, 1, 1), f32(B, T, 1)
+    return make_batch_windows(store, wt, args)
+
+
+def batch_mode(args):
+    """TURN (train.py:64-68), ALL (train.py:69-73) or SOLO (train.py:57-58)"""
+    if args['turn_based_training'] and not args['observation']:
+        return 0
+    return 1 if args['turn_based_training'] else 2
+
+
+def make_batch_windows(store, windows, args, out=None):
+    """make_batch over device windows: `windows` is the (B,8) int32 CUDA tensor of
+    `b200rl_select_windows` / `_make_batch_device` (slot, first_it lo/hi, len, start, total, winner, solo).
+    `out` may carry the tensors of a previous call of the same shape to be overwritten in place."""
+    env = store.env
+    dev = env.device
+    B, T = int(windows.shape[0]), int(args['forward_steps'])
+    mode = batch_mode(args)
+    Po = 2 if mode == 1 else 1
+    Pv = 1 if mode == 2 else 2
+    ret_tab = _return_table_dev(args['gamma'], -0.01 if env.has_reward else None, env.max_steps + 1, dev)
+    if out is None:
+        f32 = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+        obs_main = f32(B, T, Po, *env.obs_shape)
+        obs_scalar = f32(B, T, Po, *env.scalar_shape) if env.scalar_shape else None
+        out = {
+            'observation': {'scalar': obs_scalar, 'board': obs_main} if obs_scalar is not None else obs_main,
+            'policy': f32(B, T, Po, env.A), 'value': f32(B, T, Pv, 1),
+            'action': torch.empty(B, T, Po, 1, dtype=torch.int64, device=dev), 'outcome': f32(B, 1, Pv, 1),
+            'reward': f32(B, T, Pv, 1), 'return': f32(B, T, Pv, 1),
+            'episode_mask': f32(B, T, 1, 1),
+            'turn_mask': f32(B, T, Pv, 1), 'observation_mask': f32(B, T, Pv, 1),
+            'action_mask': f32(B, T, Po, env.A),
+            'progress': f32(B, T, 1),
+        }
+    obs = out['observation']
+    obs_main, obs_scalar = (obs['board'], obs['scalar']) if isinstance(obs, dict) else (obs, None)
     with torch.cuda.device(dev):
         _lib.call("b200rl_make_batch", env.game, _ptr(store.traj), store.D, store.N, _ptr(store.values),
-                  _ptr(store.logits), _ptr(wt), B, T, mode, 1 if args['observation'] else 0, _ptr(ret_tab),
-                  ret_tab.numel(), _ptr(obs_main), _ptr(obs_scalar), _ptr(policy), _ptr(amask), _ptr(action),
-                  _ptr(value), _ptr(reward), _ptr(ret), _ptr(outcome), _ptr(emask), _ptr(tmask), _ptr(omask),
-                  _ptr(progress), _lib.stream_ptr())
-    obs = {'scalar': obs_scalar, 'board': obs_main} if obs_scalar is not None else obs_main
-    return {
-        'observation': obs,
-        'policy': policy, 'value': value,
-        'action': action, 'outcome': outcome,
-        'reward': reward, 'return': ret,
-        'episode_mask': emask,
-        'turn_mask': tmask, 'observation_mask': omask,
-        'action_mask': amask,
-        'progress': progress,
-    }
+                  _ptr(store.logits), _ptr(windows), B, T, mode, 1 if args['observation'] else 0, _ptr(ret_tab),
+                  ret_tab.numel(), _ptr(obs_main), _ptr(obs_scalar), _ptr(out['policy']), _ptr(out['action_mask']),
+                  _ptr(out['action']), _ptr(out['value']), _ptr(out['reward']), _ptr(out['return']),
+                  _ptr(out['outcome']), _ptr(out['episode_mask']), _ptr(out['turn_mask']),
+                  _ptr(out['observation_mask']), _ptr(out['progress']), _lib.stream_ptr())
+    return out
 
 
 def make_batch(episodes, args):

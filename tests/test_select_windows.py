@@ -1,0 +1,123 @@
+"""select_episode (handyrl/train.py:284-302): device kernel vs the Python restatement with the same
+counter RNG (bit-exact), the host (numpy) selector's invariants, and the whole device pipeline
+rollout -> select_windows -> make_batch_windows against per-episode make_batch."""
+import numpy as np
+import pytest
+
+from oracle import select_np
+
+ARGS = {'turn_based_training': True, 'observation': False, 'gamma': 0.8, 'forward_steps': 16, 'compress_steps': 4,
+        'maximum_episodes': 3000}
+
+
+def _fake_table(n, E, rng, it_now):
+    """finished-episode rows with increasing end_it, as the rollout kernels write them"""
+    tab = np.zeros((E, 4), dtype=np.int32)
+    end = np.sort(rng.integers(50, it_now, size=n))
+    for k in range(n):
+        steps = int(rng.integers(3, 203))
+        steps = min(steps, int(end[k]) + 1)
+        tab[k % E] = (rng.integers(0, 512), steps | (int(rng.integers(1, 4)) << 16), int(end[k]), 0)
+    return tab
+
+
+def test_host_selector_invariants():
+    from handyrl_b200.train import select_windows_host
+    rng = np.random.default_rng(0)
+    rows = _fake_table(5000, 5000, rng, 4000)
+    win = select_windows_host(rows, 20000, dict(ARGS, maximum_episodes=5000), rng, it_now=4000, depth=1024)
+    steps = rows[:, 1] & 0xFFFF
+    first_it = rows[:, 2] + 1 - steps
+    assert win.shape == (20000, 8) and win.dtype == np.int32
+    ln, st, tot = win[:, 3], win[:, 4], win[:, 5]
+    assert np.all(ln >= 1) and np.all(ln <= 16) and np.all(st >= 0) and np.all(st + ln <= tot)
+    assert np.all((ln == 16) | (tot < 16) | (st + ln == tot))
+    assert np.all(4000 - (win[:, 1] - st) <= 1024)           # only episodes still in the ring
+    # recency bias: acceptance rises linearly with the index (train.py:287), so newer rows are drawn more often
+    alive_idx = np.nonzero(4000 - first_it <= 1024)[0]
+    key = {(int(r[0]), int(r[2])): i for i, r in enumerate(rows)}
+    sel = np.array([key[(int(w[0]), int(w[1] - w[4] + w[5] - 1))] for w in win[:4000]])
+    assert set(sel) <= set(alive_idx.tolist())
+    assert sel.mean() > alive_idx.mean()
+
+
+def test_python_restatement_is_deterministic_and_valid():
+    rng = np.random.default_rng(1)
+    tab = _fake_table(700, 1024, rng, 3000)
+    w1 = select_np.select_windows(tab, 700, 500, 16, 99, 0, 3000, 4096, 64)
+    w2 = select_np.select_windows(tab, 700, 500, 16, 99, 0, 3000, 4096, 64)
+    assert np.array_equal(w1, w2)
+    assert np.all(w1[:, 3] >= 1) and np.all(w1[:, 4] + w1[:, 3] <= w1[:, 5])
+    assert not np.array_equal(w1, select_np.select_windows(tab, 700, 500, 16, 99, 4, 3000, 4096, 64))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("game,plies,D", [('Geister', 700, 1024), ('TicTacToe', 60, 64), ('Geister', 900, 256)])
+def test_device_select_matches_restatement(game, plies, D):
+    import torch
+    from handyrl_b200.generation import BatchGenerator
+    gen = BatchGenerator(game, 256, seed=5, depth=D, max_episodes=4096)
+    gen.rollout(plies)
+    a = dict(ARGS, maximum_episodes=1000)
+    Bw = 512
+    w = gen.select_windows(Bw, a, seed=77).cpu().numpy()
+    tab = gen.store.ep_table.cpu().numpy()
+    cur = int(gen.store.counters[5].item())
+    assert cur > 0
+    ref = select_np.select_windows(tab, cur, 1000, 16, 77 ^ 0x5E1EC7, 0, gen.store.it, D, Bw)
+    assert np.array_equal(w, ref)
+    # a second call advances the draw counter
+    w2 = gen.select_windows(Bw, a, seed=77).cpu().numpy()
+    ref2 = select_np.select_windows(tab, cur, 1000, 16, 77 ^ 0x5E1EC7, 256, gen.store.it, D, Bw)
+    assert np.array_equal(w2, ref2) and not np.array_equal(w, w2)
+    # every selected window lies inside the ring
+    first = w[:, 1].astype(np.int64)
+    assert np.all(gen.store.it - (first - w[:, 4]) <= D)
+
+
+@pytest.mark.gpu
+def test_select_before_any_episode_finished_gives_padded_windows():
+    import torch
+    from handyrl_b200.generation import BatchGenerator
+    from handyrl_b200.train import make_batch_windows
+    gen = BatchGenerator('Geister', 64, seed=1, depth=64)
+    gen.rollout(4)
+    w = gen.select_windows(8, ARGS)
+    assert np.array_equal(w.cpu().numpy(), np.tile(np.array([0, 0, 0, 0, 0, 1, 3, 0], np.int32), (8, 1)))
+    b = make_batch_windows(gen.store, w, ARGS)
+    assert float(b['episode_mask'].sum()) == 0 and float(b['progress'].min()) == 1.0
+    assert float(b['action_mask'].min()) == float(np.float32(1e32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("game", ['Geister', 'TicTacToe'])
+def test_device_pipeline_equals_per_episode_make_batch(game):
+    """windows drawn on the device and batched in one launch == the same windows fed to make_batch as
+    episode dicts (which tests/test_make_batch_gpu.py pins to the reference)"""
+    import torch
+    from handyrl_b200.generation import BatchGenerator
+    from handyrl_b200.train import make_batch, make_batch_windows
+    gen = BatchGenerator(game, 128, seed=3, depth=1024, max_episodes=8192)
+    gen.rollout(500 if game == 'Geister' else 40)
+    eps = gen.episodes()
+    assert len(eps) > 20
+    by_key = {(e['moment'].slot, e['moment'].first_it): e for e in eps}
+    w = gen.select_windows(96, ARGS)
+    got = make_batch_windows(gen.store, w, ARGS)
+    wins = []
+    for row in w.cpu().numpy():
+        first = int(np.uint32(row[1])) | (int(np.uint32(row[2])) << 32)
+        ep = by_key[(int(row[0]), first - int(row[4]))]
+        assert ep['steps'] == int(row[5])
+        wins.append({'args': {}, 'outcome': ep['outcome'], 'moment': ep['moment'], 'base': 0, 'start': int(row[4]),
+                     'end': int(row[4] + row[3]), 'total': int(row[5])})
+    ref = make_batch(wins, ARGS)
+
+    def cmp(a, b, name):
+        if isinstance(a, dict):
+            for k in a:
+                cmp(a[k], b[k], name + '.' + k)
+        else:
+            assert torch.equal(a, b), name
+    for k in ref:
+        cmp(got[k], ref[k], k)
