@@ -8,7 +8,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200rl.so")
+# B200RL_LIB selects another build of the same library (kernel A/B experiments)
+LIB_PATH = os.environ.get("B200RL_LIB") or os.path.join(_HERE, "libb200rl.so")
 
 _lib = None
 
@@ -56,6 +57,8 @@ SIGNATURES = {
                            c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr],
     "b200rl_env_step_record": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_int, c_ptr, c_i64, c_u64, c_ptr, c_i64,
                                c_ptr, c_ptr, c_ptr],
+    "b200rl_env_sample_record": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_u64, c_u64, c_ptr, c_i64, c_u64, c_ptr, c_i64,
+                                 c_ptr, c_ptr, c_ptr, c_ptr],
     "b200rl_make_batch": [c_int, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_int, c_ptr,
                           c_i64] + [c_ptr] * 14,
     "b200rl_select_windows": [c_ptr, c_i64, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_i64, c_ptr, c_i64, c_ptr],

@@ -67,6 +67,101 @@ k_step_record(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, c
 }
 
 // ---------------------------------------------------------------------------
+// sample + step + record: the acting half of one self-play ply with a real policy
+// (handyrl/generation.py:48-61).  For every game: legal_actions in the reference's list
+// order, p = logits[legal] (the 1e32 mask only removes the others), weights = softmax(p)
+// as util.py:61-63 (fp32 exp(p - max) / sum), then random.choices' rule: cumulative weights
+// accumulated in double, first index whose cumulative weight exceeds u * total.  The chosen
+// action is applied and recorded exactly like k_step_record.
+// ---------------------------------------------------------------------------
+template <class G>
+__device__ __forceinline__ int sample_from_logits(const typename G::State& s, const float* __restrict__ lg, double u) {
+    int ids[G::LMAX];
+    const int n = G::legal_list(s, ids);
+    if (n <= 0) return -1;
+    float m = -INFINITY;
+    for (int k = 0; k < n; ++k) m = fmaxf(m, lg[ids[k]]);
+    float sum = 0.f;
+    for (int k = 0; k < n; ++k) sum = __fadd_rn(sum, expf(__fsub_rn(lg[ids[k]], m)));
+    double total = 0.0;
+    for (int k = 0; k < n; ++k) total += (double)__fdiv_rn(expf(__fsub_rn(lg[ids[k]], m)), sum);
+    const double x = u * total;
+    double cum = 0.0;
+    int pick = n - 1;
+    for (int k = 0; k < n; ++k) {
+        cum += (double)__fdiv_rn(expf(__fsub_rn(lg[ids[k]], m)), sum);
+        if (x < cum) { pick = k; break; }   // bisect_right(cum_weights, x)
+    }
+    return ids[pick];
+}
+
+template <class G>
+__global__ void __launch_bounds__(BLK)
+k_sample_record(uint32_t* state, int64_t N, const float* __restrict__ logits, const double* __restrict__ u_in,
+                uint64_t seed, uint64_t game_id_base, uint4* traj, int64_t D, uint64_t it, int32_t* ep_table,
+                int64_t E, unsigned long long* counters, int32_t* __restrict__ out_action,
+                uint8_t* __restrict__ out_terminal) {
+    const int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
+    if (i >= N) return;
+    typename G::State s = G::load(state, N, i);
+    if (G::terminal(s)) G::reset(s);  // generation.py:27: a finished slot starts its next episode
+    constexpr int PL = G::SIMULTANEOUS ? 2 : 1;  // players acting per ply
+    const uint32_t r = b200rl_rand32(seed, game_id_base + (uint64_t)i, it);
+    int acts[2] = {-1, -1};
+#pragma unroll
+    for (int q = 0; q < PL; ++q) {
+        double u;
+        if (u_in) u = u_in[i * PL + q];
+        else {  // 53 random bits like random.random()
+            const uint64_t hi = b200rl_rand32(seed ^ 0xA5A5A5A5ull, game_id_base + (uint64_t)i, it * 2 + q);
+            const uint64_t lo = b200rl_rand32(seed ^ 0x5A5A5A5Aull, game_id_base + (uint64_t)i, it * 2 + q);
+            u = (double)(((hi << 32) | lo) >> 11) * (1.0 / 9007199254740992.0);
+        }
+        acts[q] = sample_from_logits<G>(s, logits + (i * PL + q) * G::A, u);
+    }
+    const int selp = G::SIMULTANEOUS ? (int)((r >> 7) & 1) : 0;   // parallel_tictactoe.py:22
+    const int a = G::SIMULTANEOUS ? acts[selp] : acts[0];
+    const bool first = G::steps(s) == 0;
+    uint32_t rec[8];
+    G::pack_record(s, rec);
+    G::step(s, a, selp);
+    const bool term = G::terminal(s);
+    float o0 = 0.f, o1 = 0.f;
+    if (term) G::outcome(s, o0, o1);
+    const uint32_t wincode = term ? (o0 > 0 ? 1u : (o1 > 0 ? 2u : 3u)) : 0u;
+    rec[5] = ((uint32_t)a & 0xFFFF) | ((uint32_t)(selp & 1) << 16) | ((first ? 1u : 0u) << 24) |
+             ((term ? 1u : 0u) << 25) | (wincode << 26);
+    rec[6] = (uint32_t)G::steps(s);
+    rec[7] = G::SIMULTANEOUS ? (((uint32_t)acts[0] & 0xFF) | (((uint32_t)acts[1] & 0xFF) << 8)) : 0u;
+    if (traj) {
+        uint4* base = traj + (int64_t)(it % (uint64_t)D) * 2 * N;
+        base[i] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
+        base[N + i] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
+    }
+    if (counters) {
+        atomicAdd(&counters[1], 1ull);
+        if (term) {
+            atomicAdd(&counters[0], 1ull);
+            atomicAdd(&counters[1 + wincode], 1ull);
+            if (ep_table) {
+                unsigned long long idx = atomicAdd(&counters[5], 1ull);
+                int32_t* e = ep_table + (int64_t)(idx % (unsigned long long)E) * 4;
+                e[0] = (int32_t)i;
+                e[1] = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
+                e[2] = (int32_t)(uint32_t)it;
+                e[3] = (int32_t)(uint32_t)(it >> 32);
+            }
+        }
+    }
+    if (out_action) {
+#pragma unroll
+        for (int q = 0; q < PL; ++q) out_action[i * PL + q] = acts[q];
+    }
+    if (out_terminal) out_terminal[i] = term ? 1 : 0;
+    G::store(state, N, i, s);
+}
+
+// ---------------------------------------------------------------------------
 // make_batch
 // ---------------------------------------------------------------------------
 enum { MB_TURN = 0, MB_ALL = 1, MB_SOLO = 2 };
@@ -369,6 +464,21 @@ extern "C" int b200rl_env_step_record(int game, void* state, int64_t N, const in
                             (uint32_t*)state, N, actions, selected, both, auto_reset, (uint4*)traj, D, it, ep_table,
                             E, (unsigned long long*)counters, out_terminal)));
     return b200rl_check_launch("k_step_record");
+}
+
+extern "C" int b200rl_env_sample_record(int game, void* state, int64_t N, const float* logits, const double* u,
+                                        uint64_t seed, uint64_t game_id_base, void* traj, int64_t D, uint64_t it,
+                                        int32_t* ep_table, int64_t E, uint64_t* counters, int32_t* out_action,
+                                        uint8_t* out_terminal, void* stream) {
+    B200RL_REQUIRE(state && logits, "env_sample_record: null state/logits");
+    B200RL_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)traj % 16) == 0, "env_sample_record: 16-byte alignment");
+    B200RL_REQUIRE(!traj || D >= 1, "env_sample_record: trajectory ring depth D must be >= 1");
+    B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_sample_record: episode table needs E >= 1 and counters");
+    if (N <= 0) return B200RL_OK;
+    DISPATCH_GAME(game, (k_sample_record<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(
+                            (uint32_t*)state, N, logits, u, seed, game_id_base, (uint4*)traj, D, it, ep_table, E,
+                            (unsigned long long*)counters, out_action, out_terminal)));
+    return b200rl_check_launch("k_sample_record");
 }
 
 extern "C" int b200rl_make_batch(int game, const void* traj, int64_t D, int64_t N, const float* values,

@@ -1,0 +1,326 @@
+// Row-per-thread target recursion with a cp.async shared-memory pipeline (sm_100a).
+//
+// Fast path of b200rl_target_scan for the layouts compute_loss actually produces
+// (handyrl/train.py:218-258): P in {1,2}, values / rewards contiguous (B,T,P), rhos / cs either
+// (B,T,1) broadcast over players (turn-based training) or (B,T,P), T % 4 == 0, 16-byte aligned.
+//
+// One WARP owns a tile of 32 batch rows and walks it backward in chunks of TC = 16 timesteps.
+// Chunks are fetched with 16-byte cp.async (coalesced along the rows, no register staging) into a
+// warp-private ring of NS stages, so the loads of chunk k-1 .. k-NS+1 are in flight while chunk k
+// is scanned.  Each lane scans ONE row — P independent sequences, which gives the dependent fp32
+// chains some ILP — reading its row with conflict-free LDS.128 (row stride = TC*P+4 floats, i.e. an
+// odd number of 16-byte units) and writing targets / advantages in place; the warp then streams the
+// tile out with coalesced 128-bit stores.  No __syncthreads, no CTA-wide phases: warps drift freely,
+// and a persistent grid-stride over tiles keeps the 148 SMs evenly loaded.
+//
+// Arithmetic is the same Rec<> code as the generic kernel: bit-identical to torch fp32.
+#include "target_common.cuh"
+
+namespace {
+
+#ifndef B200RL_RTC
+#define B200RL_RTC 16
+#endif
+#ifndef B200RL_NSTAGE
+#define B200RL_NSTAGE 2
+#endif
+constexpr int RTC = B200RL_RTC;  // timesteps per chunk
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// copy rows x (tl*W/4) 16-byte units of a contiguous (B, T, W) view into a [32][RS] tile
+template <int W, int RS>
+__device__ __forceinline__ void fetch_tile(float* tile, const float* __restrict__ g, int64_t sb, int b0, int rows,
+                                           int t0, int tl, int lane) {
+    const int upr = (tl * W) >> 2;  // 16-byte units per row
+    const int total = rows * upr;
+    const float* base = g + (int64_t)b0 * sb + (int64_t)t0 * W;
+    for (int e = lane; e < total; e += 32) {
+        const int r = e / upr, q = e - r * upr;
+        cp_async16(tile + r * RS + q * 4, base + (int64_t)r * sb + q * 4);
+    }
+}
+
+template <int W, int RS>
+__device__ __forceinline__ void flush_tile(const float* tile, float* __restrict__ out, int64_t sb, int b0, int rows,
+                                           int t0, int tl, int lane) {
+    const int upr = (tl * W) >> 2;
+    const int total = rows * upr;
+    float* base = out + (int64_t)b0 * sb + (int64_t)t0 * W;
+    for (int e = lane; e < total; e += 32) {
+        const int r = e / upr, q = e - r * upr;
+        const float4 v = *reinterpret_cast<const float4*>(tile + r * RS + q * 4);
+        st_stream_f4(reinterpret_cast<float4*>(base + (int64_t)r * sb + q * 4), v);
+    }
+}
+
+// Full-chunk I/O with per-lane addressing hoisted out of the chunk loop: a (32 rows x RTC*W floats) tile is
+// U = RTC*W/4 sixteen-byte units per row, so lane l always moves unit q = l % U of rows r0 + i*RPI
+// (r0 = l / U, RPI = 32 / U): global and shared addresses advance by constants, no division or 64-bit multiply.
+template <int W>
+struct LaneIO {
+    static constexpr int U = RTC * W / 4, RPI = 32 / U;
+    int64_t off, step;  // element offset of (row b0+r0, unit q) at t = 0; RPI rows in elements
+    __device__ __forceinline__ void init(int64_t sb, int b0, int lane) {
+        off = (int64_t)(b0 + lane / U) * sb + (lane % U) * 4;
+        step = (int64_t)RPI * sb;
+    }
+};
+
+template <int W, int RS>
+__device__ __forceinline__ void fetch_full(float* tile, const float* __restrict__ g, const LaneIO<W>& io, int rows,
+                                           int t0, int lane) {
+    constexpr int U = LaneIO<W>::U, RPI = LaneIO<W>::RPI;
+    const int r0 = lane / U;
+    const float* p = g + io.off + t0 * W;
+    float* s = tile + r0 * RS + (lane % U) * 4;
+#pragma unroll
+    for (int i = 0; i < U; ++i)
+        if (r0 + i * RPI < rows) cp_async16(s + i * RPI * RS, p + i * io.step);
+}
+
+template <int W, int RS>
+__device__ __forceinline__ void flush_full(const float* tile, float* __restrict__ out, const LaneIO<W>& io, int rows,
+                                           int t0, int lane) {
+    constexpr int U = LaneIO<W>::U, RPI = LaneIO<W>::RPI;
+    const int r0 = lane / U;
+    float* p = out + io.off + t0 * W;
+    const float* s = tile + r0 * RS + (lane % U) * 4;
+#pragma unroll
+    for (int i = 0; i < U; ++i)
+        if (r0 + i * RPI < rows)
+            st_stream_f4(reinterpret_cast<float4*>(p + i * io.step), *reinterpret_cast<const float4*>(s + i * RPI * RS));
+}
+
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int NS>
+__global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntiles) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int RSV = RTC * P + 4;                 // row stride of the value / reward tiles (floats)
+    constexpr int WR = RHO_PP ? P : 1;               // floats per timestep of rho / c
+    constexpr int RSR = RTC * WR + 4;
+    constexpr int STAGE = 32 * (2 * RSV + (NEED_RHO ? 2 * RSR : 0));
+    const int lane = threadIdx.x;
+    const int64_t row_out = (int64_t)k.T * P;
+
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int b0 = tile * 32;
+        const int rows = min(32, k.B - b0);
+        const bool active = lane < rows;
+        float R[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+            R[p] = active ? k.boot[(int64_t)(b0 + lane) * k.boot_sb + (int64_t)p * k.boot_sp] : 0.f;
+        Rec<MT> rec_t[P];
+        Rec<MA> rec_a[P];
+
+        const int nchunks = (k.T + RTC - 1) / RTC;
+        LaneIO<P> io_v, io_r, io_o;
+        LaneIO<WR> io_rho, io_c;
+        io_v.init(k.v.sb, b0, lane);
+        io_o.init(row_out, b0, lane);
+        if (HAS_REW) io_r.init(k.rew.sb, b0, lane);
+        if (NEED_RHO) {
+            io_rho.init(k.rho.sb, b0, lane);
+            io_c.init(k.c.sb, b0, lane);
+        }
+        auto fetch = [&](int ch) {
+            if (ch >= 0) {
+                float* st = smem + ((nchunks - 1 - ch) % NS) * STAGE;
+                const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
+                if (tl == RTC) {
+                    fetch_full<P, RSV>(st, k.v.p, io_v, rows, t0, lane);
+                    if (HAS_REW) fetch_full<P, RSV>(st + 32 * RSV, k.rew.p, io_r, rows, t0, lane);
+                    if (NEED_RHO) {
+                        fetch_full<WR, RSR>(st + 64 * RSV, k.rho.p, io_rho, rows, t0, lane);
+                        fetch_full<WR, RSR>(st + 64 * RSV + 32 * RSR, k.c.p, io_c, rows, t0, lane);
+                    }
+                } else {
+                    fetch_tile<P, RSV>(st, k.v.p, k.v.sb, b0, rows, t0, tl, lane);
+                    if (HAS_REW) fetch_tile<P, RSV>(st + 32 * RSV, k.rew.p, k.rew.sb, b0, rows, t0, tl, lane);
+                    if (NEED_RHO) {
+                        fetch_tile<WR, RSR>(st + 64 * RSV, k.rho.p, k.rho.sb, b0, rows, t0, tl, lane);
+                        fetch_tile<WR, RSR>(st + 64 * RSV + 32 * RSR, k.c.p, k.c.sb, b0, rows, t0, tl, lane);
+                    }
+                }
+            }
+            cp_async_commit();  // one group per slot, possibly empty, keeps wait_group counting uniform
+        };
+#pragma unroll
+        for (int j = 0; j < NS - 1; ++j) fetch(nchunks - 1 - j);
+
+        for (int ch = nchunks - 1; ch >= 0; --ch) {
+            fetch(ch - (NS - 1));
+            cp_async_wait<NS - 1>();
+            __syncwarp();
+            float* st = smem + ((nchunks - 1 - ch) % NS) * STAGE;
+            const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
+            if (active) {
+                float* pv = st + lane * RSV;
+                float* pr = st + 32 * RSV + lane * RSV;
+                const float* prho = st + 64 * RSV + lane * RSR;
+                const float* pc = prho + 32 * RSR;
+                // software pipeline over the 4-timestep groups: the LDS.128 of group q-1 are issued before
+                // the dependent fp32 chain of group q (the in-place stores would otherwise pin them behind it)
+                float4 nv[P], nr[P], nrho[WR], nc[WR];
+                auto load_group = [&](int q) {
+#pragma unroll
+                    for (int u = 0; u < P; ++u) {
+                        nv[u] = *reinterpret_cast<const float4*>(pv + q * 4 * P + 4 * u);
+                        if (HAS_REW) nr[u] = *reinterpret_cast<const float4*>(pr + q * 4 * P + 4 * u);
+                    }
+                    if (NEED_RHO) {
+#pragma unroll
+                        for (int u = 0; u < WR; ++u) {
+                            nrho[u] = *reinterpret_cast<const float4*>(prho + q * 4 * WR + 4 * u);
+                            nc[u] = *reinterpret_cast<const float4*>(pc + q * 4 * WR + 4 * u);
+                        }
+                    }
+                };
+                load_group((tl >> 2) - 1);
+                for (int q = (tl >> 2) - 1; q >= 0; --q) {
+                    float v[4 * P], rw[4 * P], rho[4 * WR], cc[4 * WR];
+#pragma unroll
+                    for (int u = 0; u < P; ++u) {
+                        v[4 * u] = nv[u].x; v[4 * u + 1] = nv[u].y; v[4 * u + 2] = nv[u].z; v[4 * u + 3] = nv[u].w;
+                        if (HAS_REW) {
+                            rw[4 * u] = nr[u].x; rw[4 * u + 1] = nr[u].y; rw[4 * u + 2] = nr[u].z; rw[4 * u + 3] = nr[u].w;
+                        }
+                    }
+                    if (NEED_RHO) {
+#pragma unroll
+                        for (int u = 0; u < WR; ++u) {
+                            rho[4 * u] = nrho[u].x; rho[4 * u + 1] = nrho[u].y; rho[4 * u + 2] = nrho[u].z; rho[4 * u + 3] = nrho[u].w;
+                            cc[4 * u] = nc[u].x; cc[4 * u + 1] = nc[u].y; cc[4 * u + 2] = nc[u].z; cc[4 * u + 3] = nc[u].w;
+                        }
+                    }
+                    if (q > 0) load_group(q - 1);
+                    float tg[4 * P], ad[4 * P];
+#pragma unroll
+                    for (int j = 3; j >= 0; --j) {
+                        const bool last = (t0 + q * 4 + j) == k.T - 1;
+#pragma unroll
+                        for (int p = 0; p < P; ++p) {
+                            const int i = j * P + p;
+                            // `rewards is None` -> the reference adds the literal 0 (losses.py:23,35,44)
+                            const float r_ = HAS_REW ? rw[i] : 0.f;
+                            const float rh = NEED_RHO ? rho[RHO_PP ? i : j] : 0.f;
+                            const float c_ = NEED_RHO ? cc[RHO_PP ? i : j] : 0.f;
+                            float t1, a1, t2, a2;
+                            rec_t[p].step(last, v[i], r_, rh, c_, R[p], k, t1, a1);
+                            if (MT != MA) {
+                                rec_a[p].step(last, v[i], r_, rh, c_, R[p], k, t2, a2);
+                                a1 = a2;
+                            }
+                            tg[i] = t1;
+                            ad[i] = a1;
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < P; ++u) {
+                        *reinterpret_cast<float4*>(pv + q * 4 * P + 4 * u) =
+                            make_float4(ad[4 * u], ad[4 * u + 1], ad[4 * u + 2], ad[4 * u + 3]);
+                        *reinterpret_cast<float4*>(pr + q * 4 * P + 4 * u) =
+                            make_float4(tg[4 * u], tg[4 * u + 1], tg[4 * u + 2], tg[4 * u + 3]);
+                    }
+                }
+            }
+            __syncwarp();
+            if (tl == RTC) {
+                flush_full<P, RSV>(st + 32 * RSV, k.out_t, io_o, rows, t0, lane);
+                flush_full<P, RSV>(st, k.out_a, io_o, rows, t0, lane);
+            } else {
+                flush_tile<P, RSV>(st + 32 * RSV, k.out_t, row_out, b0, rows, t0, tl, lane);
+                flush_tile<P, RSV>(st, k.out_a, row_out, b0, rows, t0, tl, lane);
+            }
+            __syncwarp();
+        }
+    }
+}
+
+}  // namespace
+
+namespace {
+
+constexpr int NSTAGE = B200RL_NSTAGE;
+
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
+int launch_rows(const ScanParams& k, cudaStream_t st) {
+    constexpr int RSV = RTC * P + 4;
+    constexpr int RSR = RTC * (RHO_PP ? P : 1) + 4;
+    constexpr int STAGE = 32 * (2 * RSV + (NEED_RHO ? 2 * RSR : 0));
+    constexpr size_t SMEM = (size_t)NSTAGE * STAGE * sizeof(float);
+    auto kern = k_target_rows<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, NSTAGE>;
+    static int per_sm = 0;  // resident warps per SM for this instantiation
+    if (per_sm == 0) {
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, 32, SMEM) != cudaSuccess || n < 1) n = 1;
+        per_sm = n;
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int ntiles = (k.B + 31) / 32;
+    const int grid = min(ntiles, sms * per_sm);
+    kern<<<grid, 32, SMEM, st>>>(k, ntiles);
+    return b200rl_check_launch("k_target_rows");
+}
+
+template <int MT, int MA, int P>
+int launch_rows_p(const ScanParams& k, bool has_rew, bool rho_pp, cudaStream_t st) {
+    constexpr bool NR = (MT == B200RL_TARGET_VTRACE || MA == B200RL_TARGET_VTRACE);
+    if (NR && P > 1 && rho_pp) {
+        return has_rew ? launch_rows<MT, MA, P, true, NR, (NR && P > 1)>(k, st)
+                       : launch_rows<MT, MA, P, false, NR, (NR && P > 1)>(k, st);
+    }
+    return has_rew ? launch_rows<MT, MA, P, true, NR, false>(k, st) : launch_rows<MT, MA, P, false, NR, false>(k, st);
+}
+
+bool rows_ok(const View3& x, int W, int T) {  // contiguous (B, T, W), 16-byte aligned rows
+    if (x.p == nullptr) return false;
+    if (((uintptr_t)x.p % 16) != 0 || (x.sb % 4) != 0) return false;
+    if (T > 1 && x.st != W) return false;
+    if (W > 1 && x.sp != 1) return false;
+    return true;
+}
+
+}  // namespace
+
+int b200rl_launch_target_rows(int mt, int ma, const ScanParams& k, bool has_rew, cudaStream_t st) {
+    const int P = k.P;
+    if (P != 1 && P != 2) return -1;
+    if ((k.T % 4) != 0 || k.B < 1) return -1;
+    if (!rows_ok(k.v, P, k.T)) return -1;
+    if (has_rew && !rows_ok(k.rew, P, k.T)) return -1;
+    const bool need_rho = mt == B200RL_TARGET_VTRACE || ma == B200RL_TARGET_VTRACE;
+    bool rho_pp = false;
+    if (need_rho) {
+        if (k.rho.px != k.c.px) return -1;
+        rho_pp = P > 1 && k.rho.px == P;
+        const int W = rho_pp ? P : 1;
+        if (!rows_ok(k.rho, W, k.T) || !rows_ok(k.c, W, k.T)) return -1;
+        if (!rho_pp && P > 1 && (k.rho.sp != 0 || k.c.sp != 0)) return -1;
+    }
+#define CASE(A, B_)                                                                      \
+    if (mt == A && ma == B_)                                                             \
+        return P == 1 ? launch_rows_p<A, B_, 1>(k, has_rew, rho_pp, st) : launch_rows_p<A, B_, 2>(k, has_rew, rho_pp, st);
+    CASE(B200RL_TARGET_TD, B200RL_TARGET_TD)
+    CASE(B200RL_TARGET_UPGO, B200RL_TARGET_UPGO)
+    CASE(B200RL_TARGET_VTRACE, B200RL_TARGET_VTRACE)
+    CASE(B200RL_TARGET_TD, B200RL_TARGET_UPGO)
+    CASE(B200RL_TARGET_TD, B200RL_TARGET_VTRACE)
+    CASE(B200RL_TARGET_UPGO, B200RL_TARGET_TD)
+    CASE(B200RL_TARGET_UPGO, B200RL_TARGET_VTRACE)
+    CASE(B200RL_TARGET_VTRACE, B200RL_TARGET_TD)
+    CASE(B200RL_TARGET_VTRACE, B200RL_TARGET_UPGO)
+#undef CASE
+    return -1;
+}

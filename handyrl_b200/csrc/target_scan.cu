@@ -11,35 +11,12 @@
 // Arithmetic follows the reference's evaluation order exactly, one IEEE rounding
 // per torch op (no FMA contraction), so results are bit-identical to torch fp32
 // on CPU, not merely within 1e-5.
-#include "common.cuh"
-#include "../../include/b200rl.h"
+#include "target_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
 constexpr int TC = 32;  // timesteps per staged tile
-
-struct View3 {
-    const float* p;
-    int64_t sb, st, sp;
-    int px;   // 1 when the player dim is broadcast (stride 0), else P
-    int vec;  // 128-bit path allowed (contiguous along (t,p), 16B aligned rows)
-};
-
-struct ScanParams {
-    View3 v, rew, rho, c;
-    const float* boot;
-    int64_t boot_sb, boot_sp;
-    float* out_t;
-    float* out_a;
-    int B, T, P;
-    int rows;  // batch rows per CTA
-    float oml, lmb, gamma, gl;
-};
-
-__device__ __forceinline__ float max_nanprop(float a, float b) {
-    // torch.max propagates NaN; fmaxf does not.
-    return (a != a || b != b) ? __int_as_float(0x7fc00000) : fmaxf(a, b);
-}
 
 // Stage rows x (tl*px) floats of a strided view into shared memory.
 template <int NT>
@@ -114,66 +91,6 @@ __device__ __forceinline__ void store_tile(const float* __restrict__ s, float* _
         }
     }
 }
-
-// Per-sequence recurrence state.  `step` is called for t = T-1 down to 0 and
-// returns (target, advantage) for that t.
-template <int MODE>
-struct Rec;
-
-template <>
-struct Rec<B200RL_TARGET_TD> {  // losses.py:20-28
-    float G, v1;
-    __device__ __forceinline__ void step(bool last, float v, float r, float, float, float R, const ScanParams& k,
-                                         float& tgt, float& adv) {
-        if (last) {
-            G = R;
-        } else {
-            float a = __fmul_rn(k.oml, v1);
-            float b = __fmul_rn(k.lmb, G);
-            float c = __fadd_rn(a, b);
-            G = __fadd_rn(r, __fmul_rn(k.gamma, c));
-        }
-        v1 = v;
-        tgt = G;
-        adv = __fsub_rn(G, v);
-    }
-};
-
-template <>
-struct Rec<B200RL_TARGET_UPGO> {  // losses.py:31-40
-    float G, v1;
-    __device__ __forceinline__ void step(bool last, float v, float r, float, float, float R, const ScanParams& k,
-                                         float& tgt, float& adv) {
-        if (last) {
-            G = R;
-        } else {
-            float a = __fmul_rn(k.oml, v1);
-            float b = __fmul_rn(k.lmb, G);
-            float c = __fadd_rn(a, b);
-            G = __fadd_rn(r, __fmul_rn(k.gamma, max_nanprop(v1, c)));
-        }
-        v1 = v;
-        tgt = G;
-        adv = __fsub_rn(G, v);
-    }
-};
-
-template <>
-struct Rec<B200RL_TARGET_VTRACE> {  // losses.py:43-58
-    float acc, v1, vs1;
-    __device__ __forceinline__ void step(bool last, float v, float r, float rho, float c, float R,
-                                         const ScanParams& k, float& tgt, float& adv) {
-        float vt1 = last ? R : v1;
-        float vst1 = last ? R : vs1;
-        float delta = __fmul_rn(rho, __fsub_rn(__fadd_rn(r, __fmul_rn(k.gamma, vt1)), v));
-        acc = last ? delta : __fadd_rn(delta, __fmul_rn(__fmul_rn(k.gl, c), acc));
-        float vs = __fadd_rn(acc, v);
-        tgt = vs;
-        adv = __fsub_rn(__fadd_rn(r, __fmul_rn(k.gamma, vst1)), v);
-        v1 = v;
-        vs1 = vs;
-    }
-};
 
 template <int MT, int MA, int NT, bool HAS_REW, bool NEED_RHO>
 __global__ void __launch_bounds__(NT) k_target_scan(const ScanParams k) {
@@ -253,6 +170,32 @@ __global__ void k_target_mc(const float* __restrict__ v, int64_t v_sb, int64_t v
         int t = (int)(bt % T);
         int64_t b = bt / T;
         out[i] = __fsub_rn(ret[b * ret_sb + t * ret_st + p * ret_sp], v[b * v_sb + t * v_st + p * v_sp]);
+    }
+}
+
+// monte_carlo for contiguous values rows (T*P % 4 == 0): one float4 per thread; `returns` is either
+// contiguous like values (RET_FULL) or constant over time, (B,1,P) (the outcome, train.py:245).
+template <bool RET_FULL>
+__global__ void __launch_bounds__(256)
+k_target_mc_rows(const float4* __restrict__ v, int64_t v_sb4, const float* __restrict__ ret, int64_t ret_sb,
+                 int64_t ret_sp, float4* __restrict__ out, int64_t n4, int row4, int P) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = i / row4;
+        const int j4 = (int)(i - b * row4);
+        const float4 a = ld_stream_f4(v + b * v_sb4 + j4);
+        float4 r;
+        if (RET_FULL) {
+            r = ld_stream_f4(reinterpret_cast<const float4*>(ret + b * ret_sb) + j4);
+        } else {
+            const float* rb = ret + b * ret_sb;
+            const int p0 = (j4 * 4) % P;
+            int p1 = p0 + 1; if (p1 >= P) p1 -= P;
+            int p2 = p1 + 1; if (p2 >= P) p2 -= P;
+            int p3 = p2 + 1; if (p3 >= P) p3 -= P;
+            r = make_float4(rb[p0 * ret_sp], rb[p1 * ret_sp], rb[p2 * ret_sp], rb[p3 * ret_sp]);
+        }
+        st_stream_f4(out + i, make_float4(__fsub_rn(r.x, a.x), __fsub_rn(r.y, a.y), __fsub_rn(r.z, a.z),
+                                          __fsub_rn(r.w, a.w)));
     }
 }
 
@@ -362,6 +305,10 @@ extern "C" int b200rl_target_scan_fused(int mode_targets, int mode_adv, const fl
     k.lmb = (float)lmb;
     k.gamma = (float)gamma;
     k.gl = (float)(gamma * lmb);
+    // contiguous P<=2 layouts (what compute_loss produces): row-per-thread cp.async pipeline
+    static const bool force_generic = getenv("B200RL_TARGET_GENERIC") != nullptr;  // A/B switch for tools/sweep_targets.py
+    const int fast = force_generic ? -1 : b200rl_launch_target_rows(mode_targets, mode_adv, k, rewards != nullptr, (cudaStream_t)stream);
+    if (fast >= 0) return fast;
     return dispatch(mode_targets, mode_adv, k, rewards != nullptr, (cudaStream_t)stream);
 }
 
@@ -382,6 +329,24 @@ extern "C" int b200rl_target_mc(const float* values, int64_t v_sb, int64_t v_st,
     B200RL_REQUIRE(values && returns && out_adv, "target_mc: null pointer");
     int64_t n = B * T * P;
     if (n == 0) return B200RL_OK;
+    const int64_t TP = T * P;
+    const bool v_rows = (T == 1 || v_st == P) && (P == 1 || v_sp == 1) && TP % 4 == 0 && v_sb % 4 == 0 &&
+                        ((uintptr_t)values % 16) == 0 && ((uintptr_t)out_adv % 16) == 0 && P <= 1024;
+    const bool ret_full = (T == 1 || ret_st == P) && (P == 1 || ret_sp == 1) && ret_sb % 4 == 0 &&
+                          ((uintptr_t)returns % 16) == 0;
+    const bool ret_const = ret_st == 0;
+    if (v_rows && (ret_full || ret_const)) {
+        const int64_t n4 = n / 4;
+        int64_t blocks = (n4 + 255) / 256;
+        if (blocks > 148 * 16) blocks = 148 * 16;
+        if (ret_full)
+            k_target_mc_rows<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
+                (const float4*)values, v_sb / 4, returns, ret_sb, ret_sp, (float4*)out_adv, n4, (int)(TP / 4), (int)P);
+        else
+            k_target_mc_rows<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
+                (const float4*)values, v_sb / 4, returns, ret_sb, ret_sp, (float4*)out_adv, n4, (int)(TP / 4), (int)P);
+        return b200rl_check_launch("k_target_mc_rows");
+    }
     int64_t blocks = (n + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
     k_target_mc<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(values, v_sb, v_st, v_sp, returns, ret_sb, ret_st,

@@ -79,7 +79,67 @@ def _view3(x, shape3, full_shape):
     return [ctypes.c_void_p(xe.data_ptr()), sb, st, sp], xe
 
 
+def _call_on(dev, fn, *args):
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    stream = torch._C._cuda_getCurrentRawStream(idx)
+    if torch.cuda.current_device() != idx:
+        with torch.cuda.device(dev):
+            return fn(*args, stream)
+    return fn(*args, stream)
+
+
+def _v4(x, B, T, P):
+    """(ptr, stride_b, stride_t, stride_p) of a 4-D (b,t,p,1) tensor whose dims are full or 1 (broadcast)."""
+    s, st = x.shape, x.stride()
+    return (x.data_ptr(), st[0] if (s[0] == B and B > 1) else 0, st[1] if (s[1] == T and T > 1) else 0,
+            st[2] if (s[2] == P and P > 1) else 0)
+
+
+def _is4(x, B, T, P):
+    s = x.shape
+    return (len(s) == 4 and s[3] == 1 and (s[0] == B or s[0] == 1) and (s[1] == T or s[1] == 1)
+            and (s[2] == P or s[2] == 1) and x.dtype == torch.float32 and x.is_cuda)
+
+
+def _scan_4d(mode_t, mode_a, values, returns, rewards, lmb, gamma, rhos, cs):
+    """Lean argument marshalling for the shapes compute_loss produces (handyrl/train.py:245-253): every tensor
+    is 4-D (b,t,p,1) with dims full or 1.  Returns None when the inputs do not fit (general path below)."""
+    vs = values.shape
+    if len(vs) != 4 or vs[3] != 1 or values.dtype != torch.float32 or not values.is_cuda:
+        return None
+    B, T, P = vs[0], vs[1], vs[2]
+    if B == 0 or not _is4(returns, B, returns.shape[1] if returns.dim() == 4 else -1, P):
+        return None
+    need_rho = mode_t == 3 or mode_a == 3
+    if rewards is not None and not _is4(rewards, B, T, P):
+        return None
+    if need_rho and not (_is4(rhos, B, T, P) and _is4(cs, B, T, P)):
+        return None
+    v = _v4(values, B, T, P)
+    rs, rst = returns.shape, returns.stride()
+    boot_ptr = returns.data_ptr() + 4 * rst[1] * (rs[1] - 1)          # returns[:, -1]
+    boot_sb = rst[0] if (rs[0] == B and B > 1) else 0
+    boot_sp = rst[2] if (rs[2] == P and P > 1) else 0
+    r = _v4(rewards, B, T, P) if rewards is not None else (0, 0, 0, 0)
+    rho = _v4(rhos, B, T, P) if need_rho else (0, 0, 0, 0)
+    c = _v4(cs, B, T, P) if need_rho else (0, 0, 0, 0)
+    dev = values.device
+    if (B * T * P) % 4 == 0:   # one allocation, both halves 16-byte aligned
+        out = torch.empty((2, B, T, P, 1), dtype=torch.float32, device=dev)
+        out_t, out_a = out[0], out[1]
+    else:
+        out_t = torch.empty((B, T, P, 1), dtype=torch.float32, device=dev)
+        out_a = torch.empty((B, T, P, 1), dtype=torch.float32, device=dev)
+    rc = _call_on(dev, _lib.lib().b200rl_target_scan_fused, mode_t, mode_a, *v, boot_ptr, boot_sb, boot_sp, *r, *rho,
+                  *c, out_t.data_ptr(), out_a.data_ptr(), B, T, P, float(lmb), float(gamma))
+    _lib.check(rc, "b200rl_target_scan_fused")
+    return out_t, out_a
+
+
 def _scan(mode_t, mode_a, values, returns, rewards, lmb, gamma, rhos, cs):
+    res = _scan_4d(mode_t, mode_a, values, returns, rewards, lmb, gamma, rhos, cs)
+    if res is not None:
+        return res
     values = _as_f32_cuda(values, "values")
     returns = _as_f32_cuda(returns, "returns")
     need_rho = MODES["VTRACE"] in (mode_t, mode_a)
@@ -125,7 +185,24 @@ def _scan(mode_t, mode_a, values, returns, rewards, lmb, gamma, rhos, cs):
     return out_t, out_a
 
 
+def _monte_carlo_4d(values, returns):
+    vs = values.shape
+    if len(vs) != 4 or vs[3] != 1 or values.dtype != torch.float32 or not values.is_cuda or vs[0] == 0:
+        return None
+    B, T, P = vs[0], vs[1], vs[2]
+    if not _is4(returns, B, T, P):
+        return None
+    adv = torch.empty((B, T, P, 1), dtype=torch.float32, device=values.device)
+    rc = _call_on(values.device, _lib.lib().b200rl_target_mc, *_v4(values, B, T, P), *_v4(returns, B, T, P),
+                  adv.data_ptr(), B, T, P)
+    _lib.check(rc, "b200rl_target_mc")
+    return returns, adv
+
+
 def monte_carlo(values, returns):
+    res = _monte_carlo_4d(values, returns)
+    if res is not None:
+        return res
     values = _as_f32_cuda(values, "values")
     returns = _as_f32_cuda(returns, "returns")
     full = _bcast_shape(values, returns)

@@ -174,6 +174,20 @@ int b200rl_env_step_record(int game, void* state, int64_t N, const int32_t* acti
                            const int32_t* both, int auto_reset, void* traj, int64_t D, uint64_t it,
                            int32_t* ep_table, int64_t E, uint64_t* counters, uint8_t* out_terminal, void* stream);
 
+/*
+ * The acting half of one self-play ply with a real policy (generation.py:48-61) for N games:
+ * restart finished games, take legal_actions in the reference's list order, weights =
+ * softmax(logits[legal]) (util.py:61-63), draw like random.choices (cumulative weights in double,
+ * first index whose cumulative weight exceeds u * total), apply the action, write the trajectory
+ * record / episode table / counters like b200rl_env_step_record.
+ *   logits (N, PL, A) fp32, PL = 2 for ParallelTicTacToe (both players act, parallel_tictactoe.py:20-29) else 1
+ *   u      (N, PL) doubles in [0,1) or NULL (counter RNG keyed (seed, game_id_base + slot, it))
+ *   out_action (N, PL) int32, out_terminal (N) uint8; either may be NULL; traj may be NULL
+ */
+int b200rl_env_sample_record(int game, void* state, int64_t N, const float* logits, const double* u, uint64_t seed,
+                             uint64_t game_id_base, void* traj, int64_t D, uint64_t it, int32_t* ep_table, int64_t E,
+                             uint64_t* counters, int32_t* out_action, uint8_t* out_terminal, void* stream);
+
 enum { B200RL_BATCH_TURN = 0, B200RL_BATCH_ALL = 1, B200RL_BATCH_SOLO = 2 };
 
 /*

@@ -1,0 +1,84 @@
+"""compute_target sweep (BASELINE.json configs[4]): T in {32,200,1024} x B in {4096,65536} x P=2,
+all four modes + the fused V-Trace/UPGO pair, return head (rewards given) and value head (rewards None).
+Prints one JSON object; run on the GPU box:  python tools/sweep_targets.py > gpurun_out/sweep.json
+B200RL_TARGET_GENERIC=1 forces the generic strided kernel (A/B against the row-per-thread fast path)."""
+import json
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from handyrl_b200.losses import compute_target, compute_target_pair  # noqa: E402
+
+PEAK = 6548.8
+try:
+    PEAK = float(json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    pass
+# algorithmic bytes per (b,t,p) element at P=2: with rewards / without
+BYTES = {"MC": (12, 8), "TD": (16, 12), "UPGO": (16, 12), "VTRACE": (20, 16), "VTRACE+UPGO": (20, 16)}
+
+
+def bench(fn, sets, iters):
+    for i in range(3):
+        fn(sets[i % len(sets)])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        fn(sets[i % len(sets)])
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def main():
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(0)
+    out = {"peak_gbs": PEAK, "generic": bool(os.environ.get("B200RL_TARGET_GENERIC")), "rows": []}
+    Ts = [int(x) for x in os.environ.get('SWEEP_T', '32,200,1024').split(',')]
+    Bs = [int(x) for x in os.environ.get('SWEEP_B', '4096,65536').split(',')]
+    for T in Ts:
+        for B in Bs:
+            P = 2
+            n = B * T * P
+            nsets = max(2, min(8, int(300e6 // (n * 4 * 4)) + 1))   # rotate inputs past the 126 MB L2
+            sets = []
+            for _ in range(nsets):
+                v = torch.tanh(torch.randn(B, T, P, 1, device=dev, generator=g))
+                rew = torch.full((B, T, P, 1), -0.01, device=dev)
+                ret = torch.randn(B, T, P, 1, device=dev, generator=g)
+                oc = torch.randint(-1, 2, (B, 1, P, 1), device=dev, generator=g).float()
+                rho = torch.exp(0.5 * torch.randn(B, T, 1, 1, device=dev, generator=g)).clamp(0, 1)
+                sets.append((v, rew, ret, oc, rho, rho.clone()))
+            iters = 20 if n > 5e7 else 50
+            for head in ("return", "value"):
+                for mode in ("MC", "TD", "UPGO", "VTRACE", "VTRACE+UPGO"):
+                    if mode == "VTRACE+UPGO":
+                        if head == "return":
+                            fn = lambda s: compute_target_pair("VTRACE", "UPGO", s[0], s[2], s[1], 0.7, 0.8, s[4], s[5])
+                        else:
+                            fn = lambda s: compute_target_pair("VTRACE", "UPGO", s[0], s[3], None, 0.7, 1.0, s[4], s[5])
+                    elif head == "return":
+                        fn = lambda s, m=mode: compute_target(m, s[0], s[2], s[1], 0.7, 0.8, s[4], s[5])
+                    else:
+                        fn = lambda s, m=mode: compute_target(m, s[0], s[3], None, 0.7, 1.0, s[4], s[5])
+                    ms = bench(fn, sets, iters)
+                    by = BYTES[mode][0 if head == "return" else 1]
+                    gbs = n * by / (ms * 1e-3) / 1e9
+                    out["rows"].append({"T": T, "B": B, "P": P, "head": head, "mode": mode, "ms": round(ms, 4),
+                                        "elements_per_s": n / (ms * 1e-3), "bytes_per_element": by,
+                                        "GBps": round(gbs, 1), "frac_of_peak": round(gbs / PEAK, 3)})
+            del sets
+            torch.cuda.empty_cache()
+    print(json.dumps(out))
+    for r in out["rows"]:
+        print("T=%4d B=%5d %-6s %-12s %8.3f ms %7.1f Gelem/s %7.1f GB/s  %.3f" % (
+            r["T"], r["B"], r["head"], r["mode"], r["ms"], r["elements_per_s"] / 1e9, r["GBps"], r["frac_of_peak"]),
+            file=sys.stderr)
+
+
+if __name__ == "__main__":
+    main()
