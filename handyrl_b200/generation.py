@@ -59,6 +59,15 @@ class DeviceMoments:
 WIN_OUTCOME = {0: (0, 0), 1: (1, -1), 2: (-1, 1), 3: (0, 0)}
 
 
+def _map(x, fn):
+    """map over nested tuples / lists / dicts of tensors (hidden states)"""
+    if isinstance(x, (list, tuple)):
+        return type(x)(_map(y, fn) for y in x)
+    if isinstance(x, dict):
+        return {k: _map(v, fn) for k, v in x.items()}
+    return fn(x) if x is not None else None
+
+
 class BatchGenerator:
     """N concurrent self-play games on one GPU (one process per GPU; shard by `game_id_base`)."""
 
@@ -97,6 +106,68 @@ class BatchGenerator:
         st.it += 1
         env.it = st.it
         return term
+
+    # -- policy network in the loop (generation.py:31-68 with a real model) -----------------
+    def observe_turn(self, out=None):
+        """Restart finished games, then the turn player's observation + action mask of every game (the inputs of
+        `model.inference`, generation.py:36-41).  Returns the dict of `BatchedEnv.step_observe`."""
+        return self.env.step_observe(None, auto_reset=True, out=out)
+
+    def act(self, logits, values=None, u=None, out_action=None):
+        """Sample one action per game from `logits` (N, A) [(N, 2, A) for ParallelTicTacToe] like
+        generation.py:48-53, apply and record it.  `values` (N, 2) are stored beside the ring when the store
+        records them.  Returns (actions (N, PL) int32, terminal (N,) uint8)."""
+        env, st = self.env, self.store
+        N = env.N
+        PL = 2 if env.game == 1 else 1
+        if not (logits.is_cuda and logits.dtype == torch.float32 and logits.numel() == N * PL * env.A):
+            raise _lib.B200RLError("act: logits must be CUDA float32 of shape (N, %s%d)" % ("2, " if PL == 2 else "", env.A))
+        logits = logits.contiguous()
+        k = st.it % st.D
+        if st.logits is not None:
+            # the ring keeps the turn player's logits; for simultaneous games player 0's row (SOLO batches of
+            # ParallelTicTacToe re-derive the policy per player from the record, RandomModel-style)
+            st.logits[k].copy_(logits.view(N, PL, env.A)[:, 0])
+        if st.values is not None and values is not None:
+            st.values[k].copy_(values.reshape(N, 2))
+        if u is not None:
+            u = u.to(device=env.device, dtype=torch.float64).contiguous()
+        act = out_action if out_action is not None else torch.empty(N, PL, dtype=torch.int32, device=env.device)
+        term = torch.empty(N, dtype=torch.uint8, device=env.device)
+        with torch.cuda.device(env.device):
+            _lib.call("b200rl_env_sample_record", env.game, env._st(), N, _ptr(logits), _ptr(u), self.seed,
+                      self.game_id_base, _ptr(st.traj), st.D, st.it, _ptr(st.ep_table), st.E, _ptr(st.counters),
+                      _ptr(act), _ptr(term), env._stream())
+        st.it += 1
+        env.it = st.it
+        return act, term
+
+    @torch.no_grad()
+    def play(self, model, n_plies, hidden=None):
+        """n_plies plies of self-play for all games with `model(obs, hidden) -> {'policy','value'[,'hidden']}`
+        evaluated on the device (one forward per ply for all N games).  Recurrent state is zeroed for games that
+        restart.  Returns the final hidden state."""
+        env = self.env
+        out = None
+        for _ in range(int(n_plies)):
+            out = self.observe_turn(out)
+            if env.scalar_shape is not None:
+                obs = {'scalar': out['scalar'], 'board': out['main']}
+            else:
+                obs = out['main']
+            if hidden is not None:
+                fresh = (out['terminal'] != 0)   # slots restarted by observe_turn
+                hidden = _map(hidden, lambda h: h * (~fresh).view(-1, *([1] * (h.dim() - 1))).to(h.dtype))
+            o = model(obs, hidden)
+            hidden = o.get('hidden', None)
+            v = o.get('value')
+            values = None
+            if v is not None and self.store.values is not None:
+                # the net evaluates the turn player's view: store it in that player's slot (generation.py:40-44)
+                turn = out['turn'].long().view(-1, 1)
+                values = torch.zeros(env.N, 2, device=env.device).scatter_(1, turn, v.view(env.N, 1).float())
+            self.act(o['policy'].float(), values=values)
+        return hidden
 
     # -- window selection on the device (Batcher.select_episode, train.py:284-302) -------
     def select_windows(self, batch_size, args, seed=None, out=None):

@@ -1,0 +1,187 @@
+"""Loss and data-parallel learner around the CUDA target recursion.
+
+* `forward_prediction`, `compose_losses`, `compute_loss` keep the signatures and semantics of
+  handyrl/train.py:136-258; the four `compute_target` calls of train.py:248-253 collapse into one fused
+  `compute_target_pair` per head (targets of `value_target`, advantages of `policy_target`).
+* `DataParallelLearner` replaces `nn.DataParallel` (train.py:365-366) and the pickled weight hand-off to the
+  workers (train.py:613, worker.py:52) with one process per GPU: gradients are averaged with ONE all-reduce over
+  a flat fp32 bucket, parameters + buffers are broadcast from rank 0 as one flat tensor.
+  Everything else of the reference's Learner/Trainer (threads, queues, sockets) is out of scope.
+"""
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from .losses import compute_target_pair
+
+
+def _map(x, fn):
+    if isinstance(x, dict):
+        return {k: _map(v, fn) for k, v in x.items()}
+    if isinstance(x, (list, tuple)):
+        return type(x)(_map(v, fn) for v in x)
+    return fn(x) if x is not None else None
+
+
+def _zip_map(fn, *xs):
+    x0 = xs[0]
+    if isinstance(x0, dict):
+        return {k: _zip_map(fn, *[x[k] for x in xs]) for k in x0}
+    if isinstance(x0, (list, tuple)):
+        return type(x0)(_zip_map(fn, *vs) for vs in zip(*xs))
+    return fn(*xs) if x0 is not None else None
+
+
+def forward_prediction(model, hidden, batch, args):
+    """Network outputs for a (B, T, P, ...) batch, masked like handyrl/train.py:136-184."""
+    obs = batch['observation']
+    tmask, omask = batch['turn_mask'], batch['observation_mask']
+    B, T = tmask.shape[0], tmask.shape[1]
+    if hidden is None:
+        outputs = model(_map(obs, lambda o: o.reshape(-1, *o.shape[3:])), None)   # one pass over B*T*P rows
+        outputs = {k: v for k, v in outputs.items() if v is not None and k != 'hidden'}
+    else:
+        seq = {}
+        squeeze_players = args['turn_based_training'] and not args['observation']
+        for t in range(T):
+            o_t = _map(obs, lambda o: o[:, t].reshape(-1, *o.shape[3:]))
+            m_t = omask[:, t]                                                      # (B, P, 1)
+            gate = _map(hidden, lambda h: m_t.reshape(*h.shape[:2], *([1] * (h.dim() - 2))))
+            h_in = _zip_map(lambda h, m: h * m, hidden, gate)
+            if squeeze_players:
+                h_in = _map(h_in, lambda h: h.sum(1))          # only the turn player's state is non-zero
+            else:
+                h_in = _map(h_in, lambda h: h.reshape(-1, *h.shape[2:]))
+            out_t = model(o_t, h_in)
+            nxt = out_t.pop('hidden')
+            for k, v in out_t.items():
+                if v is not None:
+                    seq.setdefault(k, []).append(v)
+            nxt = _zip_map(lambda nh, h: nh.reshape(h.shape[0], -1, *h.shape[2:]), nxt, hidden)
+            hidden = _zip_map(lambda h, nh, m: h * (1 - m) + nh * m, hidden, nxt, gate)
+        outputs = {k: torch.stack(v, dim=1) for k, v in seq.items()}
+    for k in list(outputs):
+        o = outputs[k].reshape(B, T, -1, outputs[k].shape[-1])
+        if k == 'policy':
+            outputs[k] = (o * tmask).sum(2, keepdim=True) - batch['action_mask']   # turn player's logits, masked
+        else:
+            outputs[k] = o * omask
+    return outputs
+
+
+def compose_losses(outputs, log_selected_policies, total_advantages, targets, batch, args):
+    """handyrl/train.py:188-215"""
+    tmask, omask = batch['turn_mask'], batch['observation_mask']
+    losses = {}
+    dcnt = tmask.sum().item()
+    turn_adv = (total_advantages * tmask).sum(2, keepdim=True)
+    losses['p'] = (-log_selected_policies * turn_adv).sum()
+    if 'value' in outputs:
+        losses['v'] = (((outputs['value'] - targets['value']) ** 2) * omask).sum() / 2
+    if 'return' in outputs:
+        losses['r'] = (F.smooth_l1_loss(outputs['return'], targets['return'], reduction='none') * omask).sum()
+    entropy = torch.distributions.Categorical(logits=outputs['policy']).entropy() * tmask.sum(-1)
+    losses['ent'] = entropy.sum()
+    base = losses['p'] + losses.get('v', 0) + losses.get('r', 0)
+    decay = 1 - batch['progress'] * (1 - args['entropy_regularization_decay'])
+    losses['total'] = base + (entropy * decay).sum() * -args['entropy_regularization']
+    return losses, dcnt
+
+
+def compute_loss(batch, model, hidden, args):
+    """handyrl/train.py:218-258 with the target recursion on the CUDA kernels."""
+    outputs = forward_prediction(model, hidden, batch, args)
+    actions, emask = batch['action'], batch['episode_mask']
+    logp_b = F.log_softmax(batch['policy'], dim=-1).gather(-1, actions) * emask
+    logp_t = F.log_softmax(outputs['policy'], dim=-1).gather(-1, actions) * emask
+    rhos = torch.exp(logp_t.detach() - logp_b)
+    clipped_rhos = torch.clamp(rhos, 0, 1.0)      # clip_rho_threshold
+    cs = torch.clamp(rhos, 0, 1.0)                # clip_c_threshold
+    nograd = {k: v.detach() for k, v in outputs.items()}
+    if 'value' in nograd:
+        v = nograd['value']
+        if args['turn_based_training'] and v.shape[2] == 2:     # two-player zero-sum: fill in -opponent's value
+            v = (v - v.flip(2)) / (batch['observation_mask'].sum(dim=2, keepdim=True) + 1e-8)
+        nograd['value'] = v * emask + batch['outcome'] * (1 - emask)
+    targets, advantages = {}, {}
+    targets['value'], advantages['value'] = compute_target_pair(
+        args['value_target'], args['policy_target'], nograd.get('value'), batch['outcome'], None,
+        args['lambda'], 1, clipped_rhos, cs)
+    targets['return'], advantages['return'] = compute_target_pair(
+        args['value_target'], args['policy_target'], nograd.get('return'), batch['return'], batch['reward'],
+        args['lambda'], args['gamma'], clipped_rhos, cs)
+    total_advantages = clipped_rhos * sum(advantages.values())
+    return compose_losses(outputs, logp_t, total_advantages, targets, batch, args)
+
+
+# ------------------------------------------------------------------------------------------------
+# data-parallel learner: one process per GPU
+# ------------------------------------------------------------------------------------------------
+def flat_grads(params):
+    return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in params])
+
+
+def allreduce_gradients(params, group=None):
+    """Average gradients over the ranks with ONE all-reduce of a flat fp32 bucket (GeisterNet: 0.94 MB)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    params = [p for p in params if p.requires_grad]
+    bucket = flat_grads(params)
+    dist.all_reduce(bucket, op=dist.ReduceOp.SUM, group=group)
+    bucket /= dist.get_world_size(group)
+    off = 0
+    for p in params:
+        n = p.numel()
+        g = bucket[off:off + n].view_as(p)
+        if p.grad is None:
+            p.grad = g.clone()
+        else:
+            p.grad.copy_(g)
+        off += n
+
+
+def broadcast_weights(model, src=0, group=None):
+    """Parameters and buffers (BatchNorm statistics) from rank `src` to every rank as one flat broadcast."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    ts = [t for t in list(model.parameters()) + list(model.buffers()) if t.is_floating_point()]
+    flat = torch.cat([t.detach().reshape(-1).float() for t in ts])
+    dist.broadcast(flat, src=src, group=group)
+    off = 0
+    with torch.no_grad():
+        for t in ts:
+            n = t.numel()
+            t.copy_(flat[off:off + n].view_as(t))
+            off += n
+    for t in model.buffers():   # integer buffers (num_batches_tracked)
+        if not t.is_floating_point():
+            dist.broadcast(t, src=src, group=group)
+
+
+class DataParallelLearner:
+    """Optimiser step of handyrl/train.py:371-400 (Adam, lr schedule by data count, gradient clip 4.0) with
+    gradient all-reduce; every rank trains on windows of its OWN trajectory store."""
+
+    def __init__(self, model, args, group=None):
+        self.model, self.args, self.group = model, args, group
+        self.default_lr = 3e-8
+        self.data_cnt_ema = args['batch_size'] * args['forward_steps']
+        self.params = [p for p in model.parameters() if p.requires_grad]
+        lr = self.default_lr * self.data_cnt_ema
+        self.optimizer = torch.optim.Adam(self.params, lr=lr, weight_decay=1e-5) if self.params else None
+        self.steps = 0
+        broadcast_weights(model, 0, group)
+
+    def train_step(self, batch, hidden=None):
+        self.model.train()
+        losses, dcnt = compute_loss(batch, self.model, hidden, self.args)
+        self.optimizer.zero_grad()
+        losses['total'].backward()
+        allreduce_gradients(self.params, self.group)
+        torch.nn.utils.clip_grad_norm_(self.params, 4.0)
+        self.optimizer.step()
+        self.steps += 1
+        self.data_cnt_ema = self.data_cnt_ema * 0.8 + dcnt * 0.2   # reference: updated per epoch from the batch counts
+        for g in self.optimizer.param_groups:
+            g['lr'] = self.default_lr * self.data_cnt_ema / (1 + self.steps * 1e-5)
+        return {k: float(v) for k, v in losses.items()}, dcnt

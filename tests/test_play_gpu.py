@@ -1,0 +1,86 @@
+"""GPU: the acting half of a self-play ply with a real policy (generation.py:48-61) — sampling rule against
+the Python restatement for given uniforms, recording, and net-in-the-loop play feeding make_batch."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import sample_np
+
+pytestmark = pytest.mark.gpu
+ARGS = {'turn_based_training': True, 'observation': False, 'gamma': 0.8, 'forward_steps': 8, 'compress_steps': 4,
+        'maximum_episodes': 100000}
+
+
+@pytest.mark.parametrize("game,warm", [('Geister', 60), ('Geister', 1), ('TicTacToe', 3), ('CIGeister', 120)])
+def test_sampling_rule_matches_restatement(game, warm):
+    from handyrl_b200.generation import BatchGenerator
+    N = 1024
+    gen = BatchGenerator(game, N, seed=11, depth=256)
+    gen.rollout(warm)
+    gen.observe_turn()                                   # restarts finished games, like act() will
+    ids, cnt = gen.env.legal_list()
+    ids, cnt = ids.cpu().numpy(), cnt.cpu().numpy()
+    g = torch.Generator(device='cuda').manual_seed(5)
+    logits = torch.randn(N, gen.env.A, device='cuda', generator=g) * 3
+    u = torch.rand(N, dtype=torch.float64, device='cuda', generator=g)
+    act, term = gen.act(logits, u=u)
+    act, lg, uu = act.cpu().numpy()[:, 0], logits.cpu().numpy(), u.cpu().numpy()
+    bad = 0
+    for i in range(N):
+        legal = ids[i, :cnt[i]].tolist()
+        ref, cum = sample_np.choose(legal, lg[i], float(uu[i]))
+        assert act[i] in legal
+        if act[i] != ref:   # only possible when u*total sits within rounding of a cumulative-weight boundary
+            x = uu[i] * cum[-1]
+            assert min(abs(x - c) for c in cum) < 1e-6
+            bad += 1
+    assert bad <= 2
+
+
+def test_parallel_tictactoe_samples_both_players():
+    from handyrl_b200.generation import BatchGenerator
+    N = 512
+    gen = BatchGenerator('ParallelTicTacToe', N, seed=3, depth=64)
+    gen.observe_turn()
+    logits = torch.randn(N, 2, 9, device='cuda')
+    u = torch.rand(N, 2, dtype=torch.float64, device='cuda')
+    act, term = gen.act(logits, u=u)
+    assert act.shape == (N, 2) and int(act.min()) >= 0 and int(act.max()) < 9
+    rec = gen.store.traj[0, 1].cpu().numpy().view(np.uint32)       # second half of the records of iteration 0
+    landed, sel = rec[:, 1] & 0xFFFF, (rec[:, 1] >> 16) & 1
+    a = act.cpu().numpy()
+    assert np.array_equal(landed, a[np.arange(N), sel])
+    assert np.array_equal(rec[:, 3] & 0xFF, a[:, 0]) and np.array_equal((rec[:, 3] >> 8) & 0xFF, a[:, 1])
+    assert 0.3 < sel.mean() < 0.7
+
+
+@pytest.mark.parametrize("game", ['TicTacToe', 'Geister'])
+def test_play_with_network_feeds_make_batch(game):
+    from handyrl_b200 import nets
+    from handyrl_b200.generation import BatchGenerator
+    from handyrl_b200.train import make_batch_windows
+    N = 256
+    torch.manual_seed(0)
+    net = (nets.GeisterNet() if game == 'Geister' else nets.SimpleConv2dModel()).cuda().eval()
+    gen = BatchGenerator(game, N, seed=9, depth=512, max_episodes=1 << 14, record_values=True, record_logits=True)
+    hidden = None
+    if game == 'Geister':
+        hidden = net.init_hidden([N])
+        hidden = tuple([t.cuda() for t in part] for part in hidden)
+    plies = 260 if game == 'Geister' else 24
+    gen.play(net, plies, hidden)
+    st = gen.stats()
+    assert st['env_steps'] == N * plies and st['episodes'] > 0
+    assert st['episodes'] == st['wins0'] + st['wins1'] + st['draws']
+    w = gen.select_windows(64, ARGS)
+    b = make_batch_windows(gen.store, w, ARGS)
+    live = b['episode_mask'][..., 0, 0] > 0                              # (B, T)
+    assert bool(live.any())
+    # recorded behaviour policy = logits - action_mask: the chosen action is always legal (finite logit)
+    chosen = b['policy'].gather(-1, b['action'])[..., 0, 0]
+    assert bool((chosen[live] > -1e30).all())
+    assert bool((b['action_mask'].gather(-1, b['action'])[..., 0, 0][live] == 0).all())
+    # values were recorded for the turn player only
+    tm, v = b['turn_mask'][live], b['value'][live]
+    assert bool((v[tm == 0] == 0).all()) and float(v.abs().max()) <= 1.0
+    assert float(v[tm == 1].abs().sum()) > 0

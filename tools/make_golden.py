@@ -190,6 +190,56 @@ def gen_batch():
     print("batch_cases.pkl:", os.path.getsize(os.path.join(GOLD, "batch_cases.pkl")), "bytes")
 
 
+LOSS_CASES = [
+    # batch case, value_target, policy_target
+    ('ttt_turn', 'VTRACE', 'UPGO'), ('ttt_all', 'TD', 'TD'), ('ttt_long', 'MC', 'VTRACE'), ('pttt_solo', 'UPGO', 'TD'),
+    ('geister_turn', 'VTRACE', 'UPGO'), ('geister_all', 'TD', 'VTRACE'), ('geister_solo', 'UPGO', 'UPGO'),
+]
+
+
+def gen_loss():
+    """Reference compute_loss (handyrl/train.py:218-258) on the golden batches with seeded reference nets."""
+    import importlib
+    import pickle
+    import torch
+    from handyrl.model import ModelWrapper
+    from handyrl.train import compute_loss
+    with open(os.path.join(GOLD, "batch_cases.pkl"), "rb") as f:
+        cases = pickle.load(f)
+    out = {'weights': {}, 'cases': {}}
+    for name, vt, pt in LOSS_CASES:
+        c = cases[name]
+        mod = importlib.import_module('handyrl.envs.' + c['env'])
+        env = mod.Environment()
+        net_key = 'geister' if 'geister' in c['env'] else 'ttt'
+        torch.manual_seed(1234)
+        net = env.net()()   # net() returns the class (train.py:436)
+        if net_key not in out['weights']:
+            out['weights'][net_key] = {k: v.numpy().copy() for k, v in net.state_dict().items()}
+        model = ModelWrapper(net)
+        model.train()
+        args = dict(c['args'], **{'lambda': 0.7, 'value_target': vt, 'policy_target': pt,
+                                  'entropy_regularization': 0.1, 'entropy_regularization_decay': 0.1})
+        flat = c['out']
+        batch = {k: torch.from_numpy(v) for k, v in flat.items() if not k.startswith('observation.')}
+        if any(k.startswith('observation.') for k in flat):
+            batch['observation'] = {k.split('.', 1)[1]: torch.from_numpy(v) for k, v in flat.items()
+                                    if k.startswith('observation.')}
+        B, P = batch['value'].shape[0], batch['value'].shape[2]
+        hidden = model.init_hidden([B, P])
+        losses, dcnt = compute_loss(batch, model, hidden, args)
+        model.zero_grad()
+        losses['total'].backward()
+        gsq = sum(float((p.grad ** 2).sum()) for p in net.parameters() if p.grad is not None)
+        out['cases'][name + ':' + vt + ':' + pt] = {
+            'batch_case': name, 'net': net_key, 'args': args, 'dcnt': dcnt,
+            'losses': {k: float(v) for k, v in losses.items()}, 'grad_sq_norm': gsq}
+        print(name, vt, pt, {k: round(float(v), 4) for k, v in losses.items()}, dcnt, round(gsq, 3))
+    with open(os.path.join(GOLD, "loss_cases.pkl"), "wb") as f:
+        pickle.dump(out, f, protocol=4)
+    print("loss_cases.pkl:", os.path.getsize(os.path.join(GOLD, "loss_cases.pkl")), "bytes")
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     os.makedirs(GOLD, exist_ok=True)
