@@ -205,9 +205,9 @@ def main():
     import numpy as np
     import torch
     import torch.distributed as dist
-    from handyrl_b200.generation import BatchGenerator
+    from handyrl_b200.generation import BatchGenerator, HostReplayIndex
     from handyrl_b200.losses import compute_target_pair
-    from handyrl_b200.train import make_batch_windows, select_windows_host
+    from handyrl_b200.train import make_batch_windows
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -291,30 +291,17 @@ def main():
     # ---------------- e2e: the same step through the public API with the replay index on the host ----------
     e2e = None
     if not args.no_e2e:
-        cap = TRAIN_ARGS["maximum_episodes"]
-        mirror = np.zeros((0, 4), dtype=np.int32)
-        rows_pin = torch.empty(1 << 16, 4, dtype=torch.int32).pin_memory()
-        win_pin = torch.empty(B, 8, dtype=torch.int32).pin_memory()
+        # Software-pipelined like the reference's asynchronous batchers: while the GPU runs rollout k and the
+        # batch/targets of the windows chosen from rollouts <= k-1, the host reads back the finished-episode rows
+        # of rollout k and draws the next windows.
+        st = gen.store
+        torch.cuda.synchronize()
+        index = HostReplayIndex(gen, max_new_rows=1 << 15, n_threads=max(1, min(8, (os.cpu_count() or 1) // world)))
+        win_pin = [torch.empty(B, 8, dtype=torch.int32).pin_memory() for _ in range(2)]
         win_dev = torch.empty(B, 8, dtype=torch.int32, device=dev)
-        met_pin = torch.empty(4, dtype=torch.float32).pin_memory()
-        rng = np.random.default_rng(rank)
-        gen.finished_rows()  # drop what the device-resident run produced; the host index starts here
-        d2h_bytes = []
-
-        def e2e_step(k):
-            nonlocal mirror
-            gen.rollout(PLIES, waves=waves, out_action=act_w)
-            rows = gen.finished_rows(rows_pin)                                  # D2H: new finished-episode rows
-            mirror = np.concatenate([mirror, rows])[-cap:]
-            win = select_windows_host(mirror, B, TRAIN_ARGS, rng, it_now=gen.store.it, depth=gen.store.D)
-            win_pin.copy_(torch.from_numpy(win))
-            win_dev.copy_(win_pin, non_blocking=True)                           # H2D: this step's windows
-            (tv, av), (tr, ar) = step_tail(k, win_dev)
-            met = torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()])
-            met_pin.copy_(met, non_blocking=True)                               # D2H: the step's result
-            torch.cuda.current_stream().synchronize()
-            d2h_bytes.append(rows.nbytes + 8 + met_pin.numel() * 4)
-            return float(met_pin[0])
+        met_pin = torch.zeros(4, dtype=torch.float32).pin_memory()
+        ev_done = torch.cuda.Event()
+        hs = {"win": None, "slot": 0, "pending": False, "metric": 0.0, "d2h": 0}
 
         def step_tail(k, win):
             state["batch"] = batch = make_batch_windows(gen.store, win, TRAIN_ARGS, out=state["batch"])
@@ -323,14 +310,35 @@ def main():
             t2 = compute_target_pair("UPGO", "VTRACE", vr, batch["return"], batch["reward"], 0.7, 0.8, rho, c)
             return t1, t2
 
-        for k in range(3):
+        def e2e_step(k):
+            gen.rollout(PLIES, waves=waves, out_action=act_w)                   # async
+            index.fetch_async()                                                 # D2H: counters + new episode rows
+            if hs["pending"]:                                                   # D2H result of the previous step
+                ev_done.synchronize()
+                hs["metric"] = float(met_pin[0])
+                hs["pending"] = False
+            if hs["win"] is not None:
+                win_dev.copy_(hs["win"], non_blocking=True)                     # H2D: windows drawn last iteration
+                (tv, av), (tr, ar) = step_tail(k, win_dev)
+                met_pin.copy_(torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()]), non_blocking=True)
+                ev_done.record()
+                hs["pending"] = True
+            # ---- host work, overlapped with the GPU: index the new episodes, draw the next windows ----
+            index.commit()
+            hs["d2h"] = index.d2h_bytes
+            buf = win_pin[hs["slot"]]
+            hs["slot"] ^= 1
+            hs["win"] = index.select(B, TRAIN_ARGS, buf, seed=rank)
+
+        for k in range(4):
             e2e_step(k)
         barrier()
-        ksteps = max(3, min(args.steps, 10))
-        d2h_bytes.clear()
+        ksteps = max(5, min(args.steps, 20))
         t0 = time.perf_counter()
         for k in range(ksteps):
             e2e_step(k)
+        if hs["pending"]:
+            ev_done.synchronize()
         barrier()
         dt = time.perf_counter() - t0
         if world > 1:
@@ -338,11 +346,13 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt.item())
         e2e = {"value": N_GAMES * PLIES * ksteps * world / dt, "unit": "env-steps/s",
-               "h2d_bytes_per_step": int(win_pin.numel() * 4), "d2h_bytes_per_step": int(sum(d2h_bytes) / len(d2h_bytes)),
+               "h2d_bytes_per_step": int(win_dev.numel() * 4),
+               "d2h_bytes_per_step": int(hs["d2h"] + met_pin.numel() * 4),
                "steps": ksteps, "ms_per_step": dt / ksteps * 1e3,
-               "note": "BatchGenerator.rollout -> finished_rows (D2H) -> select_windows_host (numpy, host replay index) "
-                       "-> pinned H2D windows -> make_batch_windows -> compute_target_pair x2 -> D2H target summary; "
-                       "moments stay in HBM (the trajectory ring is the replay buffer), wall clock incl. host work"}
+               "note": "per step: BatchGenerator.rollout; D2H of the counters and the new finished-episode rows; "
+                       "HostReplayIndex.select (b200rl_select_windows_host, replay index on the host) overlapped with the GPU; pinned H2D of the "
+                       "windows; make_batch_windows; compute_target_pair x2; D2H of the target summary. Moments stay in "
+                       "HBM (the trajectory ring is the replay buffer). Wall clock incl. all host work."}
 
         # the same self-play driven ply by ply from HOST buffers (reference Environment-style stepping: actions
         # H2D, observation / legal bits / reward / terminal D2H every ply) — PCIe-bound by the fp32 observations

@@ -62,6 +62,7 @@ SIGNATURES = {
     "b200rl_make_batch": [c_int, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_int, c_ptr,
                           c_i64] + [c_ptr] * 14,
     "b200rl_select_windows": [c_ptr, c_i64, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_i64, c_ptr, c_i64, c_ptr],
+    "b200rl_select_windows_host": [c_ptr, c_i64, c_u64, c_i64, c_i64, c_u64, c_u64, c_u64, c_i64, c_ptr, c_i64, c_int],
     "b200rl_pad_stack": [c_ptr, c_ptr, c_ptr, ctypes.c_uint32, c_ptr, c_i64, c_i64, c_i64, c_ptr],
 }
 

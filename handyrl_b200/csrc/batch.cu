@@ -380,21 +380,18 @@ k_pad_stack(const uint32_t* __restrict__ src, const int64_t* __restrict__ off, c
 // L = min(finished, E, maximum_episodes) rows of the table in finishing order (index 0 = oldest);
 // a row whose first ply has already been overwritten in the trajectory ring is skipped like a rejected
 // draw.  Draws come from the counter RNG keyed (seed, window b, draw0 + 4*try + j).
-__global__ void __launch_bounds__(128)
-k_select_windows(const int32_t* __restrict__ ep_table, int64_t E, const unsigned long long* __restrict__ counters,
-                 int64_t maximum_episodes, int forward_steps, uint64_t seed, uint64_t draw0, uint64_t it_now,
-                 int64_t D, int32_t* __restrict__ out, int64_t B) {
-    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (b >= B) return;
-    const unsigned long long cursor = counters[5];
+// One window; shared by the device kernel and the host entry point so both give identical rows.
+__host__ __device__ inline void select_one_window(const int32_t* ep_table, int64_t E, unsigned long long cursor,
+                                                  int64_t maximum_episodes, int forward_steps, uint64_t seed,
+                                                  uint64_t draw0, uint64_t it_now, int64_t D, int64_t b, int32_t* w) {
     // the reference trims self.episodes to maximum_episodes (train.py:502-503)
-    const int64_t L = min((int64_t)min(cursor, (unsigned long long)E), maximum_episodes);
-    int32_t* w = out + b * 8;
+    int64_t L = (int64_t)(cursor < (unsigned long long)E ? cursor : (unsigned long long)E);
+    if (L > maximum_episodes) L = maximum_episodes;
     if (L <= 0) {  // nothing finished yet: an empty window (all rows padded)
         w[0] = 0; w[1] = 0; w[2] = 0; w[3] = 0; w[4] = 0; w[5] = 1; w[6] = 3; w[7] = 0;
         return;
     }
-    const int64_t n_draw = min(L, maximum_episodes);
+    const int64_t n_draw = L < maximum_episodes ? L : maximum_episodes;
     int32_t slot = 0, steps = 1, win = 3;
     uint64_t end_it = 0;
     uint32_t r2 = 0, r3 = 0;
@@ -416,12 +413,21 @@ k_select_windows(const int32_t* __restrict__ ep_table, int64_t E, const unsigned
         const bool alive = it_now - (end_it + 1 - (uint64_t)steps) <= (uint64_t)D;
         if (last_try || (alive && (double)r1 * (1.0 / 4294967296.0) < accept)) break;  // train.py:288
     }
-    const int cand = 1 + max(0, steps - forward_steps);                                  // train.py:291
-    const int st = (int)(((unsigned long long)r2 * (unsigned long long)cand) >> 32);      // train.py:292
-    const int ed = min(st + forward_steps, steps);                                       // train.py:293
+    const int cand = 1 + (steps - forward_steps > 0 ? steps - forward_steps : 0);         // train.py:291
+    const int st = (int)(((unsigned long long)r2 * (unsigned long long)cand) >> 32);       // train.py:292
+    const int ed = st + forward_steps < steps ? st + forward_steps : steps;               // train.py:293
     const uint64_t first = end_it + 1 - (uint64_t)steps + (uint64_t)st;
     w[0] = slot; w[1] = (int32_t)(uint32_t)first; w[2] = (int32_t)(uint32_t)(first >> 32);
     w[3] = ed - st; w[4] = st; w[5] = steps; w[6] = win; w[7] = (int32_t)(r3 >> 31);  // solo player, train.py:57-58
+}
+
+__global__ void __launch_bounds__(128)
+k_select_windows(const int32_t* __restrict__ ep_table, int64_t E, const unsigned long long* __restrict__ counters,
+                 int64_t maximum_episodes, int forward_steps, uint64_t seed, uint64_t draw0, uint64_t it_now,
+                 int64_t D, int32_t* __restrict__ out, int64_t B) {
+    const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    select_one_window(ep_table, E, counters[5], maximum_episodes, forward_steps, seed, draw0, it_now, D, b, out + b * 8);
 }
 
 inline int grid_for(int64_t n) { return (int)((n + BLK - 1) / BLK); }
@@ -517,6 +523,37 @@ extern "C" int b200rl_select_windows(const int32_t* ep_table, int64_t E, const u
         ep_table, E, (const unsigned long long*)counters, maximum_episodes, (int)forward_steps, seed, draw0, it_now, D,
         out_windows, B);
     return b200rl_check_launch("k_select_windows");
+}
+
+#include <thread>
+#include <vector>
+
+extern "C" int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t E, uint64_t cursor,
+                                          int64_t maximum_episodes, int64_t forward_steps, uint64_t seed,
+                                          uint64_t draw0, uint64_t it_now, int64_t D, int32_t* out_windows_host,
+                                          int64_t B, int n_threads) {
+    B200RL_REQUIRE(ep_table_host && out_windows_host, "select_windows_host: null pointer");
+    B200RL_REQUIRE(E >= 1 && D >= 1 && maximum_episodes >= 1 && forward_steps >= 1 && B >= 0,
+                   "select_windows_host: bad E/D/maximum_episodes/forward_steps/B");
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > 64) n_threads = 64;
+    auto work = [&](int64_t lo, int64_t hi) {
+        for (int64_t b = lo; b < hi; ++b)
+            select_one_window(ep_table_host, E, cursor, maximum_episodes, (int)forward_steps, seed, draw0, it_now, D, b,
+                              out_windows_host + b * 8);
+    };
+    if (n_threads == 1 || B < 4096) {
+        work(0, B);
+        return B200RL_OK;
+    }
+    std::vector<std::thread> th;
+    const int64_t per = (B + n_threads - 1) / n_threads;
+    for (int t = 0; t < n_threads; ++t) {
+        const int64_t lo = t * per, hi = lo + per < B ? lo + per : B;
+        if (lo < hi) th.emplace_back(work, lo, hi);
+    }
+    for (auto& x : th) x.join();
+    return B200RL_OK;
 }
 
 extern "C" int b200rl_pad_stack(const void* src, const int64_t* offsets, const void* fill_rows, uint32_t fill_bits,

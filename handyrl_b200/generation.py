@@ -9,6 +9,7 @@ reference's `select_episode` slicing (handyrl/train.py:294-301) works on it unch
 `handyrl_b200.train.make_batch` gathers windows straight from the ring.
 """
 import bz2
+import ctypes
 import pickle
 
 import numpy as np
@@ -54,6 +55,59 @@ class DeviceMoments:
     def alive(self):
         """True while the ring has not wrapped over this episode."""
         return self.store.it - self.first_it <= self.store.D
+
+
+class HostReplayIndex:
+    """Replay index on the host, like the reference Learner's `episodes` deque (train.py:480-503), for a
+    device-resident trajectory store: a pinned mirror of the finished-episode table.  Only these 16-byte rows
+    cross PCIe; the moments stay in the trajectory ring.  `fetch_async` enqueues the read-back behind the
+    rollout on the current stream, `commit` waits for it, `select` draws windows with the SAME rule and RNG as
+    the device kernel (`b200rl_select_windows_host`) into a pinned buffer ready for upload."""
+
+    def __init__(self, gen, max_new_rows=1 << 15, n_threads=4):
+        st = gen.store
+        self.gen, self.st = gen, st
+        self.table = torch.zeros(st.E, 4, dtype=torch.int32).pin_memory()
+        self.ctr = torch.zeros(8, dtype=torch.int64).pin_memory()
+        self.event = torch.cuda.Event()
+        self.max_new, self.n_threads = int(min(max_new_rows, st.E)), int(n_threads)
+        self.table.copy_(st.ep_table)                          # one full read-back; later only the new rows
+        self.cursor = self.read = int(st.counters[5].item())
+        self.draws = 0
+        self.d2h_bytes = 0
+
+    def _copy_rows(self, a0, n, non_blocking):
+        E = self.st.E
+        n1 = min(n, E - a0)
+        self.table[a0:a0 + n1].copy_(self.st.ep_table[a0:a0 + n1], non_blocking=non_blocking)
+        if n1 < n:
+            self.table[:n - n1].copy_(self.st.ep_table[:n - n1], non_blocking=non_blocking)
+        self.d2h_bytes += n * 16
+
+    def fetch_async(self):
+        self.d2h_bytes = 64
+        self.ctr.copy_(self.st.counters, non_blocking=True)
+        self._copy_rows(self.read % self.st.E, self.max_new, True)
+        self.event.record()
+
+    def commit(self):
+        self.event.synchronize()
+        cur = int(self.ctr[5])
+        if cur - self.read > self.max_new:          # more rows than the fixed slab: fetch the rest synchronously
+            lo = self.read + self.max_new
+            self._copy_rows(lo % self.st.E, min(cur - lo, self.st.E), False)
+        self.read = self.cursor = cur
+        return cur
+
+    def select(self, batch_size, args, out_pinned, seed=0):
+        if self.cursor <= 0:
+            raise _lib.B200RLError("HostReplayIndex.select: no finished episodes indexed yet")
+        a = int(args['maximum_episodes'])
+        _lib.call("b200rl_select_windows_host", ctypes.c_void_p(self.table.data_ptr()), self.st.E, self.cursor, a,
+                  int(args['forward_steps']), int(seed) ^ 0x5E1EC7, self.draws, self.st.it, self.st.D,
+                  ctypes.c_void_p(out_pinned.data_ptr()), int(batch_size), self.n_threads)
+        self.draws += 256
+        return out_pinned
 
 
 WIN_OUTCOME = {0: (0, 0), 1: (1, -1), 2: (-1, 1), 3: (0, 0)}

@@ -229,6 +229,16 @@ int b200rl_select_windows(const int32_t* ep_table, int64_t E, const uint64_t* co
                           int32_t* out_windows, int64_t B, void* stream);
 
 /*
+ * The same selection on the HOST (replay index kept in host memory, like the reference's Learner): identical
+ * rule, RNG and output as b200rl_select_windows, so the rows are bit-identical for equal arguments.
+ * ep_table_host / out_windows_host are host pointers (pin them for the upload); `cursor` = episodes finished so
+ * far (counters[5]); n_threads host threads share the B windows.
+ */
+int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t E, uint64_t cursor, int64_t maximum_episodes,
+                               int64_t forward_steps, uint64_t seed, uint64_t draw0, uint64_t it_now, int64_t D,
+                               int32_t* out_windows_host, int64_t B, int n_threads);
+
+/*
  * Padding + stacking step of make_batch (train.py:92-122) for episodes that were decoded on the
  * host (reference wire format): `src` holds the windows of all B episodes back to back, rows of
  * `row_words` 32-bit words, episode b owning rows offsets[b]..offsets[b+1]; out is (B, T, row)

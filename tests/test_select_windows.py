@@ -121,3 +121,39 @@ def test_device_pipeline_equals_per_episode_make_batch(game):
             assert torch.equal(a, b), name
     for k in ref:
         cmp(got[k], ref[k], k)
+
+
+def test_host_entry_point_matches_restatement():
+    """b200rl_select_windows_host is a HOST function of the C-ABI library: same rule and RNG as the device kernel"""
+    import ctypes
+    from handyrl_b200 import _lib
+    rng = np.random.default_rng(3)
+    for (n, E, cur, max_eps, T, D, B, thr) in [(700, 1024, 700, 500, 16, 4096, 300, 1), (1024, 1024, 5000, 100000, 32, 600, 9000, 4),
+                                               (5, 64, 5, 10, 8, 4096, 64, 2)]:
+        tab = _fake_table(n, E, rng, 3000)
+        out = np.zeros((B, 8), dtype=np.int32)
+        _lib.call("b200rl_select_windows_host", ctypes.c_void_p(tab.ctypes.data), E, cur, max_eps, T, 99, 8, 3000, D,
+                  ctypes.c_void_p(out.ctypes.data), B, thr)
+        ref = select_np.select_windows(tab, cur, max_eps, T, 99, 8, 3000, D, B)
+        assert np.array_equal(out, ref)
+
+
+@pytest.mark.gpu
+def test_host_replay_index_equals_device_selection():
+    import torch
+    from handyrl_b200.generation import BatchGenerator, HostReplayIndex
+    gen = BatchGenerator('Geister', 512, seed=5, depth=1024, max_episodes=4096)
+    gen.rollout(300)
+    idx = HostReplayIndex(gen, max_new_rows=64, n_threads=2)      # small slab: forces the synchronous top-up path
+    for _ in range(3):
+        gen.rollout(100)
+        idx.fetch_async()
+        idx.commit()
+    assert idx.cursor == int(gen.store.counters[5].item()) > 0
+    assert torch.equal(idx.table[:min(idx.cursor, gen.store.E)], gen.store.ep_table.cpu()[:min(idx.cursor, gen.store.E)])
+    a = dict(ARGS, maximum_episodes=2000)
+    pin = torch.empty(256, 8, dtype=torch.int32).pin_memory()
+    host = idx.select(256, a, pin, seed=7).clone()
+    gen._draws = 0
+    dev = gen.select_windows(256, a, seed=7).cpu()
+    assert torch.equal(host, dev)
