@@ -128,42 +128,58 @@ def workload_config(n_gpus):
 # ---------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the C oracle port on the host cores
 # ---------------------------------------------------------------------------------------------
-def cpu_hotpath(seconds_target, seed):
-    """One bounded sample of the hot path on all host cores through the oracle port (oracle/)."""
+CPU_GAMES_PER_THREAD = 256
+
+
+def cpu_hotpath_runner(seed):
+    """The whole hot path on all host cores through the C oracle port (oracle/hotpath_oracle.c): per thread
+    256 Geister games x PLIES plies -> select_episode + make_batch (B = 256*PLIES/T windows) -> UPGO/V-Trace
+    targets for both heads.  Returns (runner, cores) with the replay lists pre-filled (untimed)."""
     from oracle import games_c
     cores = os.cpu_count() or 1
-    t0 = time.perf_counter()
-    n = games_c.selfplay("geister", 20000, seed=seed, n_threads=cores)
-    rate = n / (time.perf_counter() - t0)
-    per_thread = max(20000, int(rate * seconds_target / cores))
-    t0 = time.perf_counter()
-    n = games_c.selfplay("geister", per_thread, seed=seed + 1, n_threads=cores)
-    dt = time.perf_counter() - t0
-    return n, dt, cores, per_thread
+    hp = games_c.HotPath(CPU_GAMES_PER_THREAD, PLIES, T, cores, replay_cap=1024, seed=seed)
+    for _ in range(8):      # Geister games last ~157 plies: let every thread finish episodes before timing
+        hp.step()
+    return hp, cores
+
+
+def cpu_sample_text(cores, steps, dt):
+    return ("%d steps x %d pthreads x (%d Geister games x %d plies -> select_episode + make_batch of %d windows x "
+            "T=%d -> UPGO targets + V-Trace advantages, value and return heads), C oracle port, no bz2/pickle, %.1f s"
+            % (steps, cores, CPU_GAMES_PER_THREAD, PLIES, CPU_GAMES_PER_THREAD * PLIES // T, T, dt))
 
 
 def cpu_baseline(seconds_target=12.0):
-    n, dt, cores, per_thread = cpu_hotpath(seconds_target, 1)
+    hp, cores = cpu_hotpath_runner(1)
+    t0 = time.perf_counter()
+    n = hp.step()[0]
+    per_step = time.perf_counter() - t0
+    steps = max(3, int(seconds_target / max(per_step, 1e-3)))
+    p0 = hp.phase_seconds()
+    t0 = time.perf_counter()
+    n = sum(hp.step()[0] for _ in range(steps))
+    dt = time.perf_counter() - t0
+    p1 = hp.phase_seconds()
+    ph = [(y - x) for x, y in zip(p0, p1)]
+    tot = sum(ph) or 1.0
     return {"value": n / dt, "unit": "env-steps/s", "cores": cores, "kind": "port",
-            "sample": "%d Geister env-steps per thread x %d pthreads of the C oracle (obs + action_mask + policy + "
-                      "uniform action + play per ply; batch assembly and targets not included), %.1f s"
-                      % (per_thread, cores, dt)}
+            "sample": cpu_sample_text(cores, steps, dt),
+            "phase_share": {"generation": ph[0] / tot, "make_batch": ph[1] / tot, "targets": ph[2] / tot}}
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference is pure Python and cannot travel to the GPU box; the timed arm is
-    the CPU oracle port (C restatement of the same per-ply work) on all host cores."""
+    """--impl reference: the reference is pure Python and cannot travel to the GPU box (in the build container it
+    runs ~5.4 k Geister plies/s/process); the timed arm is the C oracle port of the same step on
+    all host cores."""
     if rank != 0:
         return
-    from oracle import games_c
-    cores = os.cpu_count() or 1
-    per_thread = 150000
+    hp, cores = cpu_hotpath_runner(0)
     for _ in range(args.warmup):
-        games_c.selfplay("geister", 20000, seed=0, n_threads=cores)
+        hp.step()
     t0 = time.perf_counter()
     total = 0
     for k in range(args.steps):
-        total += games_c.selfplay("geister", per_thread, seed=10 + k, n_threads=cores)
+        total += hp.step()[0]
     dt = time.perf_counter() - t0
     v = total / dt
     line = {
@@ -172,10 +188,7 @@ def run_reference(args, rank, world):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32 cell arrays -> f32",
         "data": "synthetic", "config": workload_config(args.gpus),
         "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                         "sample": "%d env-steps per thread x %d pthreads per step (C oracle orc_selfplay: obs + "
-                                   "action_mask + policy + uniform action + play per ply; the batch-assembly and "
-                                   "target phases of the GPU arm's step are NOT run here, which favours this arm)"
-                                   % (per_thread, cores)},
+                         "sample": cpu_sample_text(cores, args.steps, dt)},
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

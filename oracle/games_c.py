@@ -99,3 +99,58 @@ def selfplay(game, n_steps_per_thread, seed=0, n_threads=1):
     cs = ctypes.c_double(0)
     return int(lib().orc_selfplay(g, ctypes.c_int64(n_steps_per_thread), ctypes.c_uint64(seed), n_threads,
                                   ctypes.byref(cs)))
+
+
+# ---- whole hot path on the CPU (oracle/hotpath_oracle.c): timed baseline of bench.py --impl reference ----
+_hp = None
+
+
+def _hotpath_lib():
+    global _hp
+    if _hp is None:
+        path = os.path.join(_HERE, "libhotpath_oracle.so")
+        if not os.path.exists(path):
+            import subprocess
+            subprocess.check_call(["make", "-C", _HERE])
+        h = ctypes.CDLL(path)
+        h.orc_hotpath_create.restype = ctypes.c_void_p
+        h.orc_hotpath_create.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint64,
+                                         ctypes.c_int]
+        h.orc_hotpath_step.restype = ctypes.c_int64
+        h.orc_hotpath_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        _hp = h
+    return _hp
+
+
+class HotPath:
+    """G Geister games per thread: generation -> select_episode + make_batch -> UPGO/V-Trace targets, per step."""
+
+    def __init__(self, games_per_thread, plies, T, n_threads, replay_cap=256, seed=0):
+        self.h = _hotpath_lib()
+        self.G, self.plies, self.T, self.n_threads = games_per_thread, plies, T, n_threads
+        self.ctx = self.h.orc_hotpath_create(games_per_thread, plies, T, replay_cap, seed, n_threads)
+
+    def step(self):
+        out = (ctypes.c_int64 * 2)()
+        n = self.h.orc_hotpath_step(self.ctx, out)
+        return int(n), int(out[0]), int(out[1])
+
+    def phase_seconds(self):
+        """cumulative thread-seconds spent in (generation, batching, targets)"""
+        out = (ctypes.c_double * 3)()
+        self.h.orc_hotpath_phase_seconds(ctypes.c_void_p(self.ctx), out)
+        return [float(x) for x in out]
+
+    def peek(self):
+        """thread 0's arrays: dict of numpy views (value-head / return-head targets and their inputs)"""
+        fp = ctypes.POINTER(ctypes.c_float)
+        ptrs = [fp() for _ in range(7)]
+        B = ctypes.c_int(0)
+        self.h.orc_hotpath_peek(ctypes.c_void_p(self.ctx), *[ctypes.byref(p) for p in ptrs], ctypes.byref(B))
+        B, T = B.value, self.T
+        n = B * T
+        arr = lambda p, k: np.ctypeslib.as_array(p, shape=(k,)).copy()
+        tv, adv, v = arr(ptrs[0], n * 4), arr(ptrs[1], n * 4), arr(ptrs[2], n * 4)
+        return dict(B=B, T=T, tv=tv.reshape(2, B, T, 2, 1), adv=adv.reshape(2, B, T, 2, 1), v=v.reshape(2, B, T, 2, 1),
+                    rho=arr(ptrs[3], n).reshape(B, T, 1, 1), outcome=arr(ptrs[4], B * 2).reshape(B, 1, 2, 1),
+                    ret=arr(ptrs[5], n * 2).reshape(B, T, 2, 1), reward=arr(ptrs[6], n * 2).reshape(B, T, 2, 1))

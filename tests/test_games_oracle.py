@@ -64,3 +64,28 @@ def test_c_random_tapes_are_self_consistent(env):
 
 def test_selfplay_baseline_driver_runs():
     assert games_c.selfplay('geister', 2000, seed=1, n_threads=2) == 4000
+
+
+def test_hotpath_port_targets_match_numpy_oracle():
+    """oracle/hotpath_oracle.c (the timed CPU baseline of bench.py) against oracle/targets_np.py, bit-exact"""
+    import numpy as np
+    from oracle import games_c, targets_np
+    hp = games_c.HotPath(32, 32, 16, 2, replay_cap=128, seed=4)
+    steps = cells = 0
+    for _ in range(10):
+        n, c, fin = hp.step()
+        steps += n
+        cells += c
+    assert steps == 10 * 2 * 32 * 32 and cells == steps and fin > 0
+    d = hp.peek()
+    tv, _ = targets_np.upgo(d['v'][0], d['outcome'], None, 0.7, 1.0)
+    _, adv = targets_np.vtrace(d['v'][0], d['outcome'], None, 0.7, 1.0, d['rho'], d['rho'])
+    assert np.array_equal(tv, d['tv'][0]) and np.array_equal(adv, d['adv'][0])
+    tv, _ = targets_np.upgo(d['v'][1], d['ret'], d['reward'], 0.7, 0.8)
+    _, adv = targets_np.vtrace(d['v'][1], d['ret'], d['reward'], 0.7, 0.8, d['rho'], d['rho'])
+    assert np.array_equal(tv, d['tv'][1]) and np.array_equal(adv, d['adv'][1])
+    # batch columns: rewards are -0.01 on live rows and 0 on padding; returns follow generation.py:73-77
+    assert set(np.unique(d['reward']).tolist()) <= {0.0, float(np.float32(-0.01))}
+    assert float(d['ret'].min()) >= -0.05 - 1e-6 and float(d['ret'].max()) <= 0.0
+    assert set(np.unique(d['outcome']).tolist()) <= {-1.0, 0.0, 1.0}
+    assert sum(hp.phase_seconds()) > 0
