@@ -76,7 +76,8 @@ def test_hotpath_port_targets_match_numpy_oracle():
         n, c, fin = hp.step()
         steps += n
         cells += c
-    assert steps == 10 * 2 * 32 * 32 and cells == steps and fin > 0
+    # no windows are cut before the first episode finishes; afterwards every generated ply is batched once
+    assert steps == 10 * 2 * 32 * 32 and c == 2 * 32 * 32 and cells <= steps and fin > 0
     d = hp.peek()
     tv, _ = targets_np.upgo(d['v'][0], d['outcome'], None, 0.7, 1.0)
     _, adv = targets_np.vtrace(d['v'][0], d['outcome'], None, 0.7, 1.0, d['rho'], d['rho'])
