@@ -47,9 +47,7 @@ k_step_record(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, c
              ((term ? 1u : 0u) << 25) | (wincode << 26);
     rec[6] = (uint32_t)G::steps(s);
     rec[7] = both ? (((uint32_t)both[2 * i] & 0xFF) | (((uint32_t)both[2 * i + 1] & 0xFF) << 8)) : 0u;
-    uint4* base = traj + (int64_t)(it % (uint64_t)D) * 2 * N;
-    base[i] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
-    base[N + i] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
+    st_record(traj, D, N, it, i, rec);
     if (term && counters) {
         atomicAdd(&counters[0], 1ull);
         atomicAdd(&counters[1 + wincode], 1ull);
@@ -133,11 +131,7 @@ k_sample_record(uint32_t* state, int64_t N, const float* __restrict__ logits, co
              ((term ? 1u : 0u) << 25) | (wincode << 26);
     rec[6] = (uint32_t)G::steps(s);
     rec[7] = G::SIMULTANEOUS ? (((uint32_t)acts[0] & 0xFF) | (((uint32_t)acts[1] & 0xFF) << 8)) : 0u;
-    if (traj) {
-        uint4* base = traj + (int64_t)(it % (uint64_t)D) * 2 * N;
-        base[i] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
-        base[N + i] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
-    }
+    if (traj) st_record(traj, D, N, it, i, rec);
     if (counters) {
         atomicAdd(&counters[1], 1ull);
         if (term) {
@@ -236,9 +230,8 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
         if (live) {
             const uint64_t it = ((uint64_t)(uint32_t)w[1] | ((uint64_t)(uint32_t)w[2] << 32)) + (uint64_t)t;
             const int64_t slot = w[0];
-            const uint4* base = p.traj + (int64_t)(it % (uint64_t)p.D) * 2 * p.N;
-            const uint4 r0 = base[slot], r1 = base[p.N + slot];
-            uint32_t rec[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+            uint32_t rec[8];
+            ld_record(p.traj, p.D, p.N, it, slot, rec);
             typename G::State s = G::unpack_record(rec);
             const int tp = G::turn(s);  // m['turn'][0]
             const bool parallel = G::SIMULTANEOUS;
@@ -463,7 +456,7 @@ extern "C" int b200rl_env_step_record(int game, void* state, int64_t N, const in
                                       int64_t D, uint64_t it, int32_t* ep_table, int64_t E, uint64_t* counters,
                                       uint8_t* out_terminal, void* stream) {
     B200RL_REQUIRE(state && actions && traj && D >= 1, "env_step_record: null state/actions/traj or D < 1");
-    B200RL_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)traj % 16) == 0, "env_step_record: 16-byte alignment");
+    B200RL_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)traj % 32) == 0, "env_step_record: 16-byte alignment");
     B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_step_record: episode table needs E >= 1 and counters");
     if (N <= 0) return B200RL_OK;
     DISPATCH_GAME(game, (k_step_record<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(
@@ -477,7 +470,7 @@ extern "C" int b200rl_env_sample_record(int game, void* state, int64_t N, const 
                                         int32_t* ep_table, int64_t E, uint64_t* counters, int32_t* out_action,
                                         uint8_t* out_terminal, void* stream) {
     B200RL_REQUIRE(state && logits, "env_sample_record: null state/logits");
-    B200RL_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)traj % 16) == 0, "env_sample_record: 16-byte alignment");
+    B200RL_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)traj % 32) == 0, "env_sample_record: 16-byte alignment");
     B200RL_REQUIRE(!traj || D >= 1, "env_sample_record: trajectory ring depth D must be >= 1");
     B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_sample_record: episode table needs E >= 1 and counters");
     if (N <= 0) return B200RL_OK;

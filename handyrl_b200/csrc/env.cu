@@ -225,7 +225,7 @@ struct RolloutParams {
     float* out_amask;   // [waves][N][A] or null
     int32_t* out_action;  // [waves][N] or null
     int64_t waves;
-    uint4* traj;        // [D][2][N] compact records or null
+    uint4* traj;        // [D][N] 32-byte compact records or null
     int64_t D;
     int32_t* ep_table;  // [E][4] = slot, steps | win << 16, end_it lo, end_it hi
     int64_t E;
@@ -293,9 +293,7 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                          ((term ? 1u : 0u) << 25) | (wincode << 26);
                 rec[6] = (uint32_t)G::steps(s);
                 rec[7] = 0;
-                uint4* base = p.traj + (int64_t)(it % (uint64_t)p.D) * 2 * p.N;
-                base[i] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
-                base[p.N + i] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
+                st_record(p.traj, p.D, p.N, it, i, rec);
             }
             if (term) {
                 n_ep += 1;
@@ -443,8 +441,8 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
                                   int32_t* ep_table, int64_t E, uint64_t* counters, void* stream) {
     REQ_STATE(state, N);
     B200RL_REQUIRE(n_plies >= 0, "env_rollout: negative n_plies");
-    B200RL_REQUIRE(aligned16(out_main) && aligned16(out_scalar) && aligned16(out_amask) && aligned16(traj),
-                   "env_rollout: outputs must be 16-byte aligned");
+    B200RL_REQUIRE(aligned16(out_main) && aligned16(out_scalar) && aligned16(out_amask) && ((uintptr_t)traj % 32) == 0,
+                   "env_rollout: outputs must be 16-byte aligned (trajectory ring: 32)");
     B200RL_REQUIRE(!(out_main || out_scalar || out_amask || out_action) || waves >= 1, "env_rollout: waves must be >= 1");
     B200RL_REQUIRE(!traj || D >= 1, "env_rollout: trajectory ring depth D must be >= 1");
     B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_rollout: episode table needs E >= 1 and counters");

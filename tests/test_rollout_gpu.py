@@ -18,7 +18,7 @@ def _rollout(env_key, N, K, chunks=1, seed=7):
     main, scalar = env.alloc_obs(waves=K)
     waves = dict(main=main, scalar=scalar, action_mask=torch.empty(K, N, env.A, device='cuda'))
     act = torch.full((K, N), -9, dtype=torch.int32, device='cuda')
-    traj = torch.zeros(K, 2, N, 4, dtype=torch.int32, device='cuda')
+    traj = torch.zeros(K, N, 8, dtype=torch.int32, device='cuda')
     ept = torch.zeros(4 * N * K // 2 + 16, 4, dtype=torch.int32, device='cuda')
     ctr = torch.zeros(8, dtype=torch.int64, device='cuda')
     per = K // chunks
@@ -36,7 +36,7 @@ def test_rollout_replays_through_oracle(env_key, N, K):
     main = waves['main'].cpu().numpy().reshape(K, N, -1)
     scalar = waves['scalar'].cpu().numpy() if geister else None
     amask = waves['action_mask'].cpu().numpy()
-    flags = traj[:, 1, :, 1].view(np.uint32)
+    flags = traj[:, :, 5].view(np.uint32)
     n_ep = 0
     wins = [0, 0, 0, 0]
     episodes = []
@@ -63,7 +63,7 @@ def test_rollout_replays_through_oracle(env_key, N, K):
             e.step(a, sel)
             steps += 1
             assert term == int(e.terminal())
-            assert int(traj[k, 1, g, 2]) == steps
+            assert int(traj[k, g, 6]) == steps
             if term:
                 oc = e.outcome()
                 code = 1 if oc[0] > 0 else (2 if oc[1] > 0 else 3)
