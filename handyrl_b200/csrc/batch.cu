@@ -190,6 +190,20 @@ struct BatchCta {
     BatchStage<G> w[WARPS];
 };
 
+// Po (1 or 2) consecutive rows per lane: the tail of a lane's last row goes to the next lane by shuffle, the
+// tail of its first row (Po == 2) is carried in registers.  bits[q] of absent rows must be zero.
+template <int NB, int RW>
+__device__ __forceinline__ void pack_rows(uint32_t* flat, int lane, int Po, int n_rows, bool valid,
+                                          const uint32_t (&bits)[2][RW]) {
+    const uint32_t t0 = flat_row_tail<NB, RW>(lane * Po, bits[0]);
+    const uint32_t t1 = Po == 2 ? flat_row_tail<NB, RW>(lane * Po + 1, bits[1]) : 0u;
+    const uint32_t carry = __shfl_up_sync(0xffffffffu, Po == 2 ? t1 : t0, 1);
+    if (!valid) return;
+    const int r0 = lane * Po;
+    flat_row_store<NB, RW>(flat, r0, bits[0], lane > 0 ? carry : 0u, r0 == n_rows - 1, t0);
+    if (Po == 2) flat_row_store<NB, RW>(flat, r0 + 1, bits[1], t0, r0 + 1 == n_rows - 1, t1);
+}
+
 template <class G>
 __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
     __shared__ BatchCta<G> cta;
@@ -294,27 +308,39 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
     constexpr int SB = G::SBITS > 0 ? G::SBITS : 1;
     const int ng = nc * Po;
     const bool rnd_policy = p.logits == nullptr;
+    // rows of >= 32 bits (Geister): shuffle-merged packing, every lane takes part (invalid lanes carry zero bits);
+    // shorter rows (TicTacToe, the 18 scalar bits): atomicOr packing after a clearing pass
+    constexpr bool BIG_O = G::OBITS >= 32, BIG_A = G::A >= 32;
     if (valid) {
         for (int q = 0; q < Po; ++q) {
             const int row = lane * Po + q;
             const bool last = row == ng - 1;
-            flat_clear_row<G::OBITS>(st.obs, row, last);
+            if (!BIG_O) flat_clear_row<G::OBITS>(st.obs, row, last);
             if (G::SBITS > 0) flat_clear_row<SB>(st.scalar, row, last);
-            flat_clear_row<G::A>(st.legal, row, last);
-            if (rnd_policy) flat_clear_row<G::A>(st.illegal, row, last);
+            if (!BIG_A) {
+                flat_clear_row<G::A>(st.legal, row, last);
+                if (rnd_policy) flat_clear_row<G::A>(st.illegal, row, last);
+            }
         }
     }
-    __syncwarp();
+    if (!BIG_O || !BIG_A || G::SBITS > 0) __syncwarp();
+    if (BIG_O) pack_rows<(BIG_O ? G::OBITS : 32), G::OW>(st.obs, lane, Po, ng, valid, ob);
+    if (BIG_A) {
+        pack_rows<(BIG_A ? G::A : 32), G::LW>(st.legal, lane, Po, ng, valid, lg);
+        if (rnd_policy) pack_rows<(BIG_A ? G::A : 32), G::LW>(st.illegal, lane, Po, ng, valid, il);
+    }
     if (valid) {
         for (int q = 0; q < Po; ++q) {
             const int row = lane * Po + q;
-            flat_put<G::OBITS, G::OW>(st.obs, row, ob[q]);
+            if (!BIG_O) flat_put<G::OBITS, G::OW>(st.obs, row, ob[q]);
             if (G::SBITS > 0) {
                 const uint32_t s1[1] = {sc[q]};
                 flat_put<SB, 1>(st.scalar, row, s1);
             }
-            flat_put<G::A, G::LW>(st.legal, row, lg[q]);
-            if (rnd_policy) flat_put<G::A, G::LW>(st.illegal, row, il[q]);
+            if (!BIG_A) {
+                flat_put<G::A, G::LW>(st.legal, row, lg[q]);
+                if (rnd_policy) flat_put<G::A, G::LW>(st.illegal, row, il[q]);
+            }
         }
     }
     __syncwarp();

@@ -52,6 +52,66 @@ __device__ __forceinline__ void flat_put(uint32_t* flat, int row, const uint32_t
     }
 }
 
+// Atomic-free packing for NB >= 32: a flat word then holds bits of at most two neighbouring rows, so the
+// partial last word ("tail") of row r is handed to row r+1 (by shuffle when the rows sit in different lanes)
+// and OR-ed into that row's first word.  No clearing pass; one __syncwarp() after the stores.
+template <int NB, int RW>
+__device__ __forceinline__ uint32_t flat_row_tail(int row, const uint32_t (&bits)[RW]) {
+    static_assert(NB >= 32, "shuffle packing needs rows of at least one word");
+    const int pos = row * NB, end = pos + NB;
+    if ((end & 31) == 0) return 0u;
+    // bits [32*wt - pos, NB) of the row, right-aligned in word wt = end >> 5
+    const int off = ((end >> 5) << 5) - pos;  // first row bit that lands in the tail word (multiple of ... any)
+    uint32_t t = 0;
+#pragma unroll
+    for (int k = 0; k < RW; ++k) {
+        const int lo = 32 * k;  // row bits [lo, lo+32) live in bits[k]
+        if (off >= lo && off < lo + 32) {
+            t = bits[k] >> (off - lo);
+            if (k + 1 < RW && off - lo > 0) t |= bits[k + 1] << (32 - (off - lo));
+        }
+    }
+    return t;
+}
+
+// Store row `row`; `carry` = tail of row-1 (0 for the first row of the tile).  The last row also stores its tail.
+template <int NB, int RW>
+__device__ __forceinline__ void flat_row_store(uint32_t* flat, int row, const uint32_t (&bits)[RW], uint32_t carry,
+                                               bool is_last_row, uint32_t tail) {
+    const int pos = row * NB;
+    const int w0 = pos >> 5, sh = pos & 31;
+    const int wt = (pos + NB) >> 5;
+    flat[w0] = (bits[0] << sh) | carry;
+#pragma unroll
+    for (int k = 1; k <= RW; ++k) {
+        const uint32_t cur = k < RW ? bits[k] : 0u;
+        if (w0 + k < wt) flat[w0 + k] = __funnelshift_l(bits[k - 1], cur, sh);
+    }
+    if (is_last_row && ((pos + NB) & 31) != 0) flat[wt] = tail;
+}
+
+// One row per lane (the env kernels).  All 32 lanes must call; lanes >= n_rows pass zero bits.
+template <int NB, int RW>
+__device__ __forceinline__ void flat_pack_warp(uint32_t* flat, int lane, int n_rows, const uint32_t (&bits)[RW]) {
+    const uint32_t tail = flat_row_tail<NB, RW>(lane, bits);
+    const uint32_t carry = __shfl_up_sync(0xffffffffu, tail, 1);
+    if (lane < n_rows) flat_row_store<NB, RW>(flat, lane, bits, lane > 0 ? carry : 0u, lane == n_rows - 1, tail);
+}
+
+// nibble -> float4 without touching shared memory (B200RL_EMIT_ALU, default): 4 predicated selects on the
+// ALU pipes instead of one LDS.128 per 16 bytes — the L1/LSU pipe, which also carries the global stores, was
+// the busiest unit with the shared-memory table (profiles/r1_step_full.md: L1/TEX 66 %, issue 29 %).
+#ifndef B200RL_EMIT_TABLE
+#define B200RL_EMIT_ALU 1
+#endif
+__device__ __forceinline__ float4 nibble_expand(uint32_t nib, const float4* __restrict__ tbl, float v0, float v1) {
+#ifdef B200RL_EMIT_ALU
+    return make_float4((nib & 1u) ? v1 : v0, (nib & 2u) ? v1 : v0, (nib & 4u) ? v1 : v0, (nib & 8u) ? v1 : v0);
+#else
+    return tbl[nib & 15u];
+#endif
+}
+
 // Stream `rows` x NB floats (tile base 16-byte aligned) from the flat bit string.
 template <int NB>
 __device__ __forceinline__ void emit_flat_f32(const uint32_t* __restrict__ flat, const float4* __restrict__ tbl,
@@ -59,19 +119,22 @@ __device__ __forceinline__ void emit_flat_f32(const uint32_t* __restrict__ flat,
     const int total = rows * NB;
     const int n4 = total >> 2;
     float4* o4 = reinterpret_cast<float4*>(out_tile);
+    // lane q always reads nibble (q & 7) of word (q >> 3) + 4*j: constant shift, constant address stride
+    const int sh = (lane & 7) << 2;
+    const uint32_t* fw = flat + (lane >> 3);
     int q = lane;
 #pragma unroll 1
     for (; q + 96 < n4; q += 128) {
         uint32_t w[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) w[u] = flat[(q + 32 * u) >> 3];
+        for (int u = 0; u < 4; ++u) w[u] = fw[(q >> 3 << 0) - (lane >> 3) + 4 * u];
         float4 f[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) f[u] = tbl[(w[u] >> (((q + 32 * u) & 7) << 2)) & 15u];
+        for (int u = 0; u < 4; ++u) f[u] = nibble_expand(w[u] >> sh, tbl, v0, v1);
 #pragma unroll
         for (int u = 0; u < 4; ++u) st_stream_f4(o4 + q + 32 * u, f[u]);
     }
-    for (; q < n4; q += 32) st_stream_f4(o4 + q, tbl[(flat[q >> 3] >> ((q & 7) << 2)) & 15u]);
+    for (; q < n4; q += 32) st_stream_f4(o4 + q, nibble_expand(flat[q >> 3] >> sh, tbl, v0, v1));
     // tail (< 4 floats) of a partial tile
     for (int e = (n4 << 2) + lane; e < total; e += 32) out_tile[e] = ((flat[e >> 5] >> (e & 31)) & 1u) ? v1 : v0;
 }

@@ -110,19 +110,32 @@ __device__ __forceinline__ void emit_views(CtaStage<G>& cta, int warp, const typ
     const bool want_obs = out_main || (G::SBITS > 0 && out_scalar);
     const bool want_legal = out_amask || out_bits;
     uint32_t ob[G::OW], sc[1] = {0}, lm[G::LW];
+#pragma unroll
+    for (int k = 0; k < G::OW; ++k) ob[k] = 0;
+#pragma unroll
+    for (int k = 0; k < G::LW; ++k) lm[k] = 0;
     if (valid) {
         if (want_obs) G::obs_bits(s, view, ob, sc[0]);
         if (want_legal) G::legal_bits(s, lm);
         const bool last = lane == ng - 1;
-        if (out_main) flat_clear_row<G::OBITS>(st.obs, lane, last);
+        if (G::OBITS < 32 && out_main) flat_clear_row<G::OBITS>(st.obs, lane, last);
         if (G::SBITS > 0 && out_scalar) flat_clear_row<SB>(st.scalar, lane, last);
-        if (out_amask) flat_clear_row<G::A>(st.legal, lane, last);
+        if (G::A < 32 && out_amask) flat_clear_row<G::A>(st.legal, lane, last);
     }
-    __syncwarp();
+    if (G::OBITS < 32 || G::SBITS > 0 || G::A < 32) __syncwarp();
+    // rows of >= 32 bits: shuffle-merged packing (all lanes participate); shorter rows: atomicOr packing
+    if (G::OBITS >= 32) {
+        if (out_main) flat_pack_warp<(G::OBITS >= 32 ? G::OBITS : 32), G::OW>(st.obs, lane, ng, ob);
+    } else if (valid && out_main) {
+        flat_put<G::OBITS, G::OW>(st.obs, lane, ob);
+    }
+    if (G::A >= 32) {
+        if (out_amask) flat_pack_warp<(G::A >= 32 ? G::A : 32), G::LW>(st.legal, lane, ng, lm);
+    } else if (valid && out_amask) {
+        flat_put<G::A, G::LW>(st.legal, lane, lm);
+    }
     if (valid) {
-        if (out_main) flat_put<G::OBITS, G::OW>(st.obs, lane, ob);
         if (G::SBITS > 0 && out_scalar) flat_put<SB, 1>(st.scalar, lane, sc);
-        if (out_amask) flat_put<G::A, G::LW>(st.legal, lane, lm);
         if (out_bits) {
 #pragma unroll
             for (int k = 0; k < G::LW; ++k) out_bits[(g0 + lane) * G::LW + k] = lm[k];
