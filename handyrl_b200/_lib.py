@@ -63,6 +63,9 @@ SIGNATURES = {
                           c_i64] + [c_ptr] * 14,
     "b200rl_select_windows": [c_ptr, c_i64, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_i64, c_ptr, c_i64, c_ptr],
     "b200rl_select_windows_host": [c_ptr, c_i64, c_u64, c_i64, c_i64, c_u64, c_u64, c_u64, c_i64, c_ptr, c_i64, c_int],
+    "b200rl_policy_terms": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_dbl, c_dbl, c_ptr, c_ptr, c_ptr, c_ptr],
+    "b200rl_policy_terms_backward": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr],
+    "b200rl_value_blend": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_int, c_ptr, c_ptr],
     "b200rl_pad_stack": [c_ptr, c_ptr, c_ptr, ctypes.c_uint32, c_ptr, c_i64, c_i64, c_i64, c_ptr],
 }
 

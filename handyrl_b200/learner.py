@@ -12,6 +12,7 @@ import torch
 import torch.distributed as dist
 import torch.nn.functional as F
 
+from . import _lib
 from .losses import compute_target_pair
 
 
@@ -88,21 +89,75 @@ def compose_losses(outputs, log_selected_policies, total_advantages, targets, ba
     return losses, dcnt
 
 
-def compute_loss(batch, model, hidden, args):
-    """handyrl/train.py:218-258 with the target recursion on the CUDA kernels."""
+def _p(t):
+    return t.data_ptr()
+
+
+class _PolicyTerms(torch.autograd.Function):
+    """log pi_t(a) * emask, clipped rho and c in one pass over the two logit rows (b200rl_policy_terms)."""
+
+    @staticmethod
+    def forward(ctx, pol_t, pol_b, actions, emask):
+        lead, A = pol_t.shape[:-1], pol_t.shape[-1]
+        rows = pol_t.numel() // A
+        pt, pb = pol_t.detach().contiguous(), pol_b.contiguous()
+        act = actions.contiguous()
+        em = emask.expand(*lead, 1).contiguous()
+        shape = tuple(lead) + (1,)
+        logp, rho, c = (torch.empty(shape, dtype=torch.float32, device=pol_t.device) for _ in range(3))
+        with torch.cuda.device(pol_t.device):
+            _lib.call("b200rl_policy_terms", _p(pb), _p(pt), _p(act), _p(em), rows, A, 1.0, 1.0, _p(logp), _p(rho),
+                      _p(c), _lib.stream_ptr())
+        ctx.save_for_backward(pt, act, em)
+        ctx.mark_non_differentiable(rho, c)
+        return logp, rho, c
+
+    @staticmethod
+    def backward(ctx, g_logp, _g_rho, _g_c):
+        pt, act, em = ctx.saved_tensors
+        A = pt.shape[-1]
+        grad = torch.empty_like(pt)
+        with torch.cuda.device(pt.device):
+            _lib.call("b200rl_policy_terms_backward", _p(pt), _p(act), _p(em), _p(g_logp.contiguous()),
+                      pt.numel() // A, A, _p(grad), _lib.stream_ptr())
+        return grad, None, None, None
+
+
+def value_blend(values, omask, emask, outcome, symmetric):
+    """train.py:236-239 in one kernel (bit-identical to the torch expression)."""
+    B, T, P = values.shape[0], values.shape[1], values.shape[2]
+    v = values.contiguous()
+    out = torch.empty_like(v)
+    with torch.cuda.device(v.device):
+        _lib.call("b200rl_value_blend", _p(v), _p(omask.contiguous()), _p(emask.contiguous()),
+                  _p(outcome.contiguous()), B, T, P, 1 if symmetric else 0, _p(out), _lib.stream_ptr())
+    return out
+
+
+def compute_loss(batch, model, hidden, args, fused=True):
+    """handyrl/train.py:218-258 with the target recursion (and, with `fused`, the policy-ratio and value-blend
+    pre-processing) on the CUDA kernels.  `fused=False` keeps the reference's torch expressions around the scan."""
     outputs = forward_prediction(model, hidden, batch, args)
     actions, emask = batch['action'], batch['episode_mask']
-    logp_b = F.log_softmax(batch['policy'], dim=-1).gather(-1, actions) * emask
-    logp_t = F.log_softmax(outputs['policy'], dim=-1).gather(-1, actions) * emask
-    rhos = torch.exp(logp_t.detach() - logp_b)
-    clipped_rhos = torch.clamp(rhos, 0, 1.0)      # clip_rho_threshold
-    cs = torch.clamp(rhos, 0, 1.0)                # clip_c_threshold
+    fused = fused and outputs['policy'].is_cuda and outputs['policy'].dtype == torch.float32
+    if fused:
+        logp_t, clipped_rhos, cs = _PolicyTerms.apply(outputs['policy'], batch['policy'], actions, emask)
+    else:
+        logp_b = F.log_softmax(batch['policy'], dim=-1).gather(-1, actions) * emask
+        logp_t = F.log_softmax(outputs['policy'], dim=-1).gather(-1, actions) * emask
+        rhos = torch.exp(logp_t.detach() - logp_b)
+        clipped_rhos = torch.clamp(rhos, 0, 1.0)      # clip_rho_threshold
+        cs = torch.clamp(rhos, 0, 1.0)                # clip_c_threshold
     nograd = {k: v.detach() for k, v in outputs.items()}
     if 'value' in nograd:
         v = nograd['value']
-        if args['turn_based_training'] and v.shape[2] == 2:     # two-player zero-sum: fill in -opponent's value
-            v = (v - v.flip(2)) / (batch['observation_mask'].sum(dim=2, keepdim=True) + 1e-8)
-        nograd['value'] = v * emask + batch['outcome'] * (1 - emask)
+        sym = bool(args['turn_based_training'] and v.shape[2] == 2)   # two-player zero-sum: fill in -opponent's value
+        if fused:
+            nograd['value'] = value_blend(v, batch['observation_mask'], emask, batch['outcome'], sym)
+        else:
+            if sym:
+                v = (v - v.flip(2)) / (batch['observation_mask'].sum(dim=2, keepdim=True) + 1e-8)
+            nograd['value'] = v * emask + batch['outcome'] * (1 - emask)
     targets, advantages = {}, {}
     targets['value'], advantages['value'] = compute_target_pair(
         args['value_target'], args['policy_target'], nograd.get('value'), batch['outcome'], None,

@@ -247,6 +247,34 @@ int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t E, uint64_t
 int b200rl_pad_stack(const void* src, const int64_t* offsets, const void* fill_rows, uint32_t fill_bits, void* out,
                      int64_t B, int64_t T, int64_t row_words, void* stream);
 
+/* ------------------------------------------------------------------ */
+/* Loss pre-processing around the recursion — handyrl/train.py:224-239  */
+/* ------------------------------------------------------------------ */
+
+/*
+ * Per row r of A logits (rows = B*T*Po, contiguous (rows, A) fp32):
+ *   out_logp_target[r] = log_softmax(policy_target[r])[action[r]] * emask[r]          (train.py:226)
+ *   ratio = exp(out_logp_target[r] - log_softmax(policy_behaviour[r])[action[r]] * emask[r])  (train.py:225-229)
+ *   out_rho[r] = clamp(ratio, 0, clip_rho), out_c[r] = clamp(ratio, 0, clip_c)         (train.py:230-231)
+ * action is int64 (rows), emask fp32 (rows) (episode_mask broadcast over players by the caller).
+ */
+int b200rl_policy_terms(const float* policy_behaviour, const float* policy_target, const int64_t* action,
+                        const float* emask, int64_t rows, int64_t A, double clip_rho, double clip_c,
+                        float* out_logp_target, float* out_rho, float* out_c, void* stream);
+
+/* Backward of out_logp_target w.r.t. policy_target: grad[r][j] = grad_logp[r] * emask[r] * ([j == a] - softmax_j). */
+int b200rl_policy_terms_backward(const float* policy_target, const int64_t* action, const float* emask,
+                                 const float* grad_logp, int64_t rows, int64_t A, float* out_grad_policy, void* stream);
+
+/*
+ * Value-head input of compute_target (train.py:236-239) on contiguous (B,T,P) fp32:
+ *   symmetric && P == 2: v <- (v + (-swap_players(v))) / (omask.sum(players) + 1e-8)
+ *   out = v * emask + outcome * (1 - emask)        emask (B,T), outcome (B,P)
+ * Same op order as the torch expression (bit-identical).
+ */
+int b200rl_value_blend(const float* values, const float* omask, const float* emask, const float* outcome, int64_t B,
+                       int64_t T, int64_t P, int symmetric, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,8 +37,9 @@ CASES = ['ttt_turn:VTRACE:UPGO', 'ttt_all:TD:TD', 'ttt_long:MC:VTRACE', 'pttt_so
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("name", CASES)
-def test_compute_loss_matches_reference(golden_dir, name):
+def test_compute_loss_matches_reference(golden_dir, name, fused):
     from handyrl_b200.learner import compute_loss
     loss, batches = _load(golden_dir)
     c = loss['cases'][name]
@@ -57,11 +58,11 @@ def test_compute_loss_matches_reference(golden_dir, name):
     if hasattr(net, 'init_hidden'):
         hidden = net.init_hidden([B, P])
         hidden = tuple([t.to(dev) for t in part] for part in hidden)
-    losses, dcnt = compute_loss(batch, net, hidden, c['args'])
+    losses, dcnt = compute_loss(batch, net, hidden, c['args'], fused=fused)
     assert dcnt == c['dcnt']
     # fp32 tolerance: GPU convolutions and reductions order differently from the CPU reference
     for k, ref in c['losses'].items():
-        assert float(losses[k]) == pytest.approx(ref, rel=2e-3, abs=2e-3), k
+        assert float(losses[k].detach()) == pytest.approx(ref, rel=2e-3, abs=2e-3), k
     net.zero_grad()
     losses['total'].backward()
     gsq = sum(float((p.grad ** 2).sum()) for p in net.parameters() if p.grad is not None)
