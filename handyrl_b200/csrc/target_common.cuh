@@ -29,24 +29,27 @@ __device__ __forceinline__ float max_nanprop(float a, float b) {
     return r;
 }
 
-// Per-sequence recurrence state.  `step` is called for t = T-1 down to 0 and
-// returns (target, advantage) for that t.
+// Per-sequence recurrence state.  `first` handles t = T-1 (the bootstrap step), `next` every earlier t in
+// descending order; both return (target, advantage) of that t.  Splitting the two keeps the hot loop free of
+// the `t == T-1` selects.
 template <int MODE>
 struct Rec;
 
 template <>
 struct Rec<B200RL_TARGET_TD> {  // losses.py:20-28
     float G, v1;
-    __device__ __forceinline__ void step(bool last, float v, float r, float, float, float R, const ScanParams& k,
-                                         float& tgt, float& adv) {
-        if (last) {
-            G = R;
-        } else {
-            float a = __fmul_rn(k.oml, v1);
-            float b = __fmul_rn(k.lmb, G);
-            float c = __fadd_rn(a, b);
-            G = __fadd_rn(r, __fmul_rn(k.gamma, c));
-        }
+    __device__ __forceinline__ void first(float v, float, float, float, float R, const ScanParams&, float& tgt,
+                                          float& adv) {
+        G = R;
+        v1 = v;
+        tgt = G;
+        adv = __fsub_rn(G, v);
+    }
+    __device__ __forceinline__ void next(float v, float r, float, float, const ScanParams& k, float& tgt, float& adv) {
+        float a = __fmul_rn(k.oml, v1);
+        float b = __fmul_rn(k.lmb, G);
+        float c = __fadd_rn(a, b);
+        G = __fadd_rn(r, __fmul_rn(k.gamma, c));
         v1 = v;
         tgt = G;
         adv = __fsub_rn(G, v);
@@ -56,16 +59,18 @@ struct Rec<B200RL_TARGET_TD> {  // losses.py:20-28
 template <>
 struct Rec<B200RL_TARGET_UPGO> {  // losses.py:31-40
     float G, v1;
-    __device__ __forceinline__ void step(bool last, float v, float r, float, float, float R, const ScanParams& k,
-                                         float& tgt, float& adv) {
-        if (last) {
-            G = R;
-        } else {
-            float a = __fmul_rn(k.oml, v1);
-            float b = __fmul_rn(k.lmb, G);
-            float c = __fadd_rn(a, b);
-            G = __fadd_rn(r, __fmul_rn(k.gamma, max_nanprop(v1, c)));
-        }
+    __device__ __forceinline__ void first(float v, float, float, float, float R, const ScanParams&, float& tgt,
+                                          float& adv) {
+        G = R;
+        v1 = v;
+        tgt = G;
+        adv = __fsub_rn(G, v);
+    }
+    __device__ __forceinline__ void next(float v, float r, float, float, const ScanParams& k, float& tgt, float& adv) {
+        float a = __fmul_rn(k.oml, v1);
+        float b = __fmul_rn(k.lmb, G);
+        float c = __fadd_rn(a, b);
+        G = __fadd_rn(r, __fmul_rn(k.gamma, max_nanprop(v1, c)));
         v1 = v;
         tgt = G;
         adv = __fsub_rn(G, v);
@@ -75,20 +80,34 @@ struct Rec<B200RL_TARGET_UPGO> {  // losses.py:31-40
 template <>
 struct Rec<B200RL_TARGET_VTRACE> {  // losses.py:43-58
     float acc, v1, vs1;
-    __device__ __forceinline__ void step(bool last, float v, float r, float rho, float c, float R,
-                                         const ScanParams& k, float& tgt, float& adv) {
-        float vt1 = last ? R : v1;
-        float vst1 = last ? R : vs1;
-        float delta = __fmul_rn(rho, __fsub_rn(__fadd_rn(r, __fmul_rn(k.gamma, vt1)), v));
-        acc = last ? delta : __fadd_rn(delta, __fmul_rn(__fmul_rn(k.gl, c), acc));
+    __device__ __forceinline__ void first(float v, float r, float rho, float, float R, const ScanParams& k,
+                                          float& tgt, float& adv) {
+        acc = __fmul_rn(rho, __fsub_rn(__fadd_rn(r, __fmul_rn(k.gamma, R)), v));   // delta[T-1]
         float vs = __fadd_rn(acc, v);
         tgt = vs;
-        adv = __fsub_rn(__fadd_rn(r, __fmul_rn(k.gamma, vst1)), v);
+        adv = __fsub_rn(__fadd_rn(r, __fmul_rn(k.gamma, R)), v);
         v1 = v;
         vs1 = vs;
     }
+    __device__ __forceinline__ void next(float v, float r, float rho, float c, const ScanParams& k, float& tgt,
+                                         float& adv) {
+        float delta = __fmul_rn(rho, __fsub_rn(__fadd_rn(r, __fmul_rn(k.gamma, v1)), v));
+        acc = __fadd_rn(delta, __fmul_rn(__fmul_rn(k.gl, c), acc));
+        float vs = __fadd_rn(acc, v);
+        tgt = vs;
+        adv = __fsub_rn(__fadd_rn(r, __fmul_rn(k.gamma, vs1)), v);
+        v1 = v;
+        vs1 = vs;
+    }
+    // kept for the generic kernel's call sites
 };
 
+template <int MODE>
+__device__ __forceinline__ void rec_step(Rec<MODE>& rec, bool last, float v, float r, float rho, float c, float R,
+                                         const ScanParams& k, float& tgt, float& adv) {
+    if (last) rec.first(v, r, rho, c, R, k, tgt, adv);
+    else rec.next(v, r, rho, c, k, tgt, adv);
+}
 
 // Row-per-thread fast path (target_rows.cu).  Returns -1 when the layout is not eligible
 // (caller falls back to the generic kernel), else a b200rl status.

@@ -100,6 +100,42 @@ __device__ __forceinline__ void flush_full(const float* tile, float* __restrict_
             st_stream_f4(reinterpret_cast<float4*>(p + i * io.step), *reinterpret_cast<const float4*>(s + i * RPI * RS));
 }
 
+// Four timesteps (descending) of the P sequences of one row.  FIRST: the group contains t = T-1 at j = 3.
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, bool FIRST>
+__device__ __forceinline__ void scan_group(const float (&v)[4 * P], const float (&rw)[4 * P],
+                                           const float (&rho)[4 * (RHO_PP ? P : 1)],
+                                           const float (&cc)[4 * (RHO_PP ? P : 1)], Rec<MT> (&rec_t)[P],
+                                           Rec<MA> (&rec_a)[P], const float (&R)[P], const ScanParams& k,
+                                           float (&tg)[4 * P], float (&ad)[4 * P]) {
+#pragma unroll
+    for (int j = 3; j >= 0; --j) {
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const int i = j * P + p;
+            // `rewards is None` -> the reference adds the literal 0 (losses.py:23,35,44)
+            const float r_ = HAS_REW ? rw[i] : 0.f;
+            const float rh = NEED_RHO ? rho[RHO_PP ? i : j] : 0.f;
+            const float c_ = NEED_RHO ? cc[RHO_PP ? i : j] : 0.f;
+            float t1, a1, t2, a2;
+            if (FIRST && j == 3) {
+                rec_t[p].first(v[i], r_, rh, c_, R[p], k, t1, a1);
+                if (MT != MA) {
+                    rec_a[p].first(v[i], r_, rh, c_, R[p], k, t2, a2);
+                    a1 = a2;
+                }
+            } else {
+                rec_t[p].next(v[i], r_, rh, c_, k, t1, a1);
+                if (MT != MA) {
+                    rec_a[p].next(v[i], r_, rh, c_, k, t2, a2);
+                    a1 = a2;
+                }
+            }
+            tg[i] = t1;
+            ad[i] = a1;
+        }
+    }
+}
+
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int NS>
 __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntiles) {
     extern __shared__ __align__(16) float smem[];
@@ -203,26 +239,10 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
                     }
                     if (q > 0) load_group(q - 1);
                     float tg[4 * P], ad[4 * P];
-#pragma unroll
-                    for (int j = 3; j >= 0; --j) {
-                        const bool last = (t0 + q * 4 + j) == k.T - 1;
-#pragma unroll
-                        for (int p = 0; p < P; ++p) {
-                            const int i = j * P + p;
-                            // `rewards is None` -> the reference adds the literal 0 (losses.py:23,35,44)
-                            const float r_ = HAS_REW ? rw[i] : 0.f;
-                            const float rh = NEED_RHO ? rho[RHO_PP ? i : j] : 0.f;
-                            const float c_ = NEED_RHO ? cc[RHO_PP ? i : j] : 0.f;
-                            float t1, a1, t2, a2;
-                            rec_t[p].step(last, v[i], r_, rh, c_, R[p], k, t1, a1);
-                            if (MT != MA) {
-                                rec_a[p].step(last, v[i], r_, rh, c_, R[p], k, t2, a2);
-                                a1 = a2;
-                            }
-                            tg[i] = t1;
-                            ad[i] = a1;
-                        }
-                    }
+                    if (t0 + q * 4 + 3 == k.T - 1)   // warp-uniform: the very first group holds the bootstrap step
+                        scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, true>(v, rw, rho, cc, rec_t, rec_a, R, k, tg, ad);
+                    else
+                        scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, false>(v, rw, rho, cc, rec_t, rec_a, R, k, tg, ad);
 #pragma unroll
                     for (int u = 0; u < P; ++u) {
                         *reinterpret_cast<float4*>(pv + q * 4 * P + 4 * u) =

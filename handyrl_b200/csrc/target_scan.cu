@@ -145,9 +145,9 @@ __global__ void __launch_bounds__(NT) k_target_scan(const ScanParams k) {
                     c = pc[tt * k.c.px];
                 }
                 float tgt, adv, tgt2, adv2;
-                rec_t.step(last, v, rw, rho, c, R, k, tgt, adv);
+                rec_step(rec_t, last, v, rw, rho, c, R, k, tgt, adv);
                 if (MT != MA) {
-                    rec_a.step(last, v, rw, rho, c, R, k, tgt2, adv2);
+                    rec_step(rec_a, last, v, rw, rho, c, R, k, tgt2, adv2);
                     adv = adv2;
                 }
                 pv[tt * P] = adv;
