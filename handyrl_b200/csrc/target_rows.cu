@@ -4,7 +4,7 @@
 // (handyrl/train.py:218-258): P in {1,2}, values / rewards contiguous (B,T,P), rhos / cs either
 // (B,T,1) broadcast over players (turn-based training) or (B,T,P), T % 4 == 0, 16-byte aligned.
 //
-// One WARP owns a tile of 32 batch rows and walks it backward in chunks of TC = 16 timesteps.
+// One WARP owns a tile of TR batch rows and walks it backward in chunks of RTC timesteps (shapes below).
 // Chunks are fetched with 16-byte cp.async (coalesced along the rows, no register staging) into a
 // warp-private ring of NS stages, so the loads of chunk k-1 .. k-NS+1 are in flight while chunk k
 // is scanned.  Each lane scans ONE row — P independent sequences, which gives the dependent fp32
@@ -18,13 +18,16 @@
 
 namespace {
 
-#ifndef B200RL_RTC
-#define B200RL_RTC 16
+#ifndef B200RL_SHORT_T
+#define B200RL_SHORT_T 64
 #endif
 #ifndef B200RL_NSTAGE
 #define B200RL_NSTAGE 2
 #endif
-constexpr int RTC = B200RL_RTC;  // timesteps per chunk
+// Tile shapes (TR batch rows per warp x RTC timesteps per chunk).  What HBM delivers for this access pattern is set
+// by the contiguous bytes fetched per row (tools/probe_rows.cu: 128 B -> 4.9 TB/s, 256 B -> 5.8 TB/s, 1 KB -> 6.0 of a
+// 6.2 TB/s streaming copy), so long rows use 16 rows x 32 steps (256 B per row at P = 2; lanes >= 16 only help
+// with the copies) and short rows, where a whole 32-row tile is one contiguous block anyway, keep 32 x 16.
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
@@ -34,6 +37,12 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+// wait until at most n (1..3, warp-uniform) commit groups are pending
+__device__ __forceinline__ void cp_async_wait_n(int n) {
+    if (n == 1) cp_async_wait<1>();
+    else if (n == 2) cp_async_wait<2>();
+    else cp_async_wait<3>();
 }
 
 // copy rows x (tl*W/4) 16-byte units of a contiguous (B, T, W) view into a [32][RS] tile
@@ -65,9 +74,10 @@ __device__ __forceinline__ void flush_tile(const float* tile, float* __restrict_
 // Full-chunk I/O with per-lane addressing hoisted out of the chunk loop: a (32 rows x RTC*W floats) tile is
 // U = RTC*W/4 sixteen-byte units per row, so lane l always moves unit q = l % U of rows r0 + i*RPI
 // (r0 = l / U, RPI = 32 / U): global and shared addresses advance by constants, no division or 64-bit multiply.
-template <int W>
+template <int W, int TR, int RTC>
 struct LaneIO {
-    static constexpr int U = RTC * W / 4, RPI = 32 / U;
+    static constexpr int U = RTC * W / 4, RPI = 32 / U, NI = TR / RPI;
+    static_assert(U <= 32 && 32 % U == 0 && TR % RPI == 0, "chunk width must divide a warp");
     int64_t off, step;  // element offset of (row b0+r0, unit q) at t = 0; RPI rows in elements
     __device__ __forceinline__ void init(int64_t sb, int b0, int lane) {
         off = (int64_t)(b0 + lane / U) * sb + (lane % U) * 4;
@@ -75,27 +85,29 @@ struct LaneIO {
     }
 };
 
-template <int W, int RS>
-__device__ __forceinline__ void fetch_full(float* tile, const float* __restrict__ g, const LaneIO<W>& io, int rows,
-                                           int t0, int lane) {
-    constexpr int U = LaneIO<W>::U, RPI = LaneIO<W>::RPI;
+template <int W, int RS, int TR, int RTC>
+__device__ __forceinline__ void fetch_full(float* tile, const float* __restrict__ g, const LaneIO<W, TR, RTC>& io,
+                                           int rows, int t0, int lane) {
+    using IO = LaneIO<W, TR, RTC>;
+    constexpr int U = IO::U, RPI = IO::RPI, NI = IO::NI;
     const int r0 = lane / U;
     const float* p = g + io.off + t0 * W;
     float* s = tile + r0 * RS + (lane % U) * 4;
 #pragma unroll
-    for (int i = 0; i < U; ++i)
+    for (int i = 0; i < NI; ++i)
         if (r0 + i * RPI < rows) cp_async16(s + i * RPI * RS, p + i * io.step);
 }
 
-template <int W, int RS>
-__device__ __forceinline__ void flush_full(const float* tile, float* __restrict__ out, const LaneIO<W>& io, int rows,
-                                           int t0, int lane) {
-    constexpr int U = LaneIO<W>::U, RPI = LaneIO<W>::RPI;
+template <int W, int RS, int TR, int RTC>
+__device__ __forceinline__ void flush_full(const float* tile, float* __restrict__ out, const LaneIO<W, TR, RTC>& io,
+                                           int rows, int t0, int lane) {
+    using IO = LaneIO<W, TR, RTC>;
+    constexpr int U = IO::U, RPI = IO::RPI, NI = IO::NI;
     const int r0 = lane / U;
     float* p = out + io.off + t0 * W;
     const float* s = tile + r0 * RS + (lane % U) * 4;
 #pragma unroll
-    for (int i = 0; i < U; ++i)
+    for (int i = 0; i < NI; ++i)
         if (r0 + i * RPI < rows)
             st_stream_f4(reinterpret_cast<float4*>(p + i * io.step), *reinterpret_cast<const float4*>(s + i * RPI * RS));
 }
@@ -136,19 +148,22 @@ __device__ __forceinline__ void scan_group(const float (&v)[4 * P], const float 
     }
 }
 
-template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int NS>
-__global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntiles) {
+// ns = ring depth (2..4 stages): 2 when the grid fills the SMs (more resident warps hide the latency better than
+// deeper rings), up to 4 when there are few tiles and each warp has to cover the DRAM latency on its own.
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int TR, int RTC>
+__global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntiles, int c_alias, int ns) {
     extern __shared__ __align__(16) float smem[];
     constexpr int RSV = RTC * P + 4;                 // row stride of the value / reward tiles (floats)
     constexpr int WR = RHO_PP ? P : 1;               // floats per timestep of rho / c
     constexpr int RSR = RTC * WR + 4;
-    constexpr int STAGE = 32 * (2 * RSV + (NEED_RHO ? 2 * RSR : 0));
+    // c_alias: cs is the same tensor as rhos (the reference clips both at 1.0, train.py:222,230-231): one tile
+    const int STAGE = TR * (2 * RSV + (NEED_RHO ? (c_alias ? RSR : 2 * RSR) : 0));
     const int lane = threadIdx.x;
     const int64_t row_out = (int64_t)k.T * P;
 
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int b0 = tile * 32;
-        const int rows = min(32, k.B - b0);
+        const int b0 = tile * TR;
+        const int rows = min(TR, k.B - b0);
         const bool active = lane < rows;
         float R[P];
 #pragma unroll
@@ -158,8 +173,8 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
         Rec<MA> rec_a[P];
 
         const int nchunks = (k.T + RTC - 1) / RTC;
-        LaneIO<P> io_v, io_r, io_o;
-        LaneIO<WR> io_rho, io_c;
+        LaneIO<P, TR, RTC> io_v, io_r, io_o;
+        LaneIO<WR, TR, RTC> io_rho, io_c;
         io_v.init(k.v.sb, b0, lane);
         io_o.init(row_out, b0, lane);
         if (HAS_REW) io_r.init(k.rew.sb, b0, lane);
@@ -169,40 +184,39 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
         }
         auto fetch = [&](int ch) {
             if (ch >= 0) {
-                float* st = smem + ((nchunks - 1 - ch) % NS) * STAGE;
+                float* st = smem + ((nchunks - 1 - ch) % ns) * STAGE;
                 const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
                 if (tl == RTC) {
-                    fetch_full<P, RSV>(st, k.v.p, io_v, rows, t0, lane);
-                    if (HAS_REW) fetch_full<P, RSV>(st + 32 * RSV, k.rew.p, io_r, rows, t0, lane);
+                    fetch_full<P, RSV, TR, RTC>(st, k.v.p, io_v, rows, t0, lane);
+                    if (HAS_REW) fetch_full<P, RSV, TR, RTC>(st + TR * RSV, k.rew.p, io_r, rows, t0, lane);
                     if (NEED_RHO) {
-                        fetch_full<WR, RSR>(st + 64 * RSV, k.rho.p, io_rho, rows, t0, lane);
-                        fetch_full<WR, RSR>(st + 64 * RSV + 32 * RSR, k.c.p, io_c, rows, t0, lane);
+                        fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV, k.rho.p, io_rho, rows, t0, lane);
+                        if (!c_alias) fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV + TR * RSR, k.c.p, io_c, rows, t0, lane);
                     }
                 } else {
                     fetch_tile<P, RSV>(st, k.v.p, k.v.sb, b0, rows, t0, tl, lane);
-                    if (HAS_REW) fetch_tile<P, RSV>(st + 32 * RSV, k.rew.p, k.rew.sb, b0, rows, t0, tl, lane);
+                    if (HAS_REW) fetch_tile<P, RSV>(st + TR * RSV, k.rew.p, k.rew.sb, b0, rows, t0, tl, lane);
                     if (NEED_RHO) {
-                        fetch_tile<WR, RSR>(st + 64 * RSV, k.rho.p, k.rho.sb, b0, rows, t0, tl, lane);
-                        fetch_tile<WR, RSR>(st + 64 * RSV + 32 * RSR, k.c.p, k.c.sb, b0, rows, t0, tl, lane);
+                        fetch_tile<WR, RSR>(st + 2 * TR * RSV, k.rho.p, k.rho.sb, b0, rows, t0, tl, lane);
+                        if (!c_alias) fetch_tile<WR, RSR>(st + 2 * TR * RSV + TR * RSR, k.c.p, k.c.sb, b0, rows, t0, tl, lane);
                     }
                 }
             }
             cp_async_commit();  // one group per slot, possibly empty, keeps wait_group counting uniform
         };
-#pragma unroll
-        for (int j = 0; j < NS - 1; ++j) fetch(nchunks - 1 - j);
+        for (int j = 0; j < ns - 1; ++j) fetch(nchunks - 1 - j);
 
         for (int ch = nchunks - 1; ch >= 0; --ch) {
-            fetch(ch - (NS - 1));
-            cp_async_wait<NS - 1>();
+            fetch(ch - (ns - 1));
+            cp_async_wait_n(ns - 1);
             __syncwarp();
-            float* st = smem + ((nchunks - 1 - ch) % NS) * STAGE;
+            float* st = smem + ((nchunks - 1 - ch) % ns) * STAGE;
             const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
             if (active) {
                 float* pv = st + lane * RSV;
-                float* pr = st + 32 * RSV + lane * RSV;
-                const float* prho = st + 64 * RSV + lane * RSR;
-                const float* pc = prho + 32 * RSR;
+                float* pr = st + TR * RSV + lane * RSV;
+                const float* prho = st + 2 * TR * RSV + lane * RSR;
+                const float* pc = c_alias ? prho : prho + TR * RSR;
                 // software pipeline over the 4-timestep groups: the LDS.128 of group q-1 are issued before
                 // the dependent fp32 chain of group q (the in-place stores would otherwise pin them behind it)
                 float4 nv[P], nr[P], nrho[WR], nc[WR];
@@ -254,10 +268,10 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
             }
             __syncwarp();
             if (tl == RTC) {
-                flush_full<P, RSV>(st + 32 * RSV, k.out_t, io_o, rows, t0, lane);
-                flush_full<P, RSV>(st, k.out_a, io_o, rows, t0, lane);
+                flush_full<P, RSV, TR, RTC>(st + TR * RSV, k.out_t, io_o, rows, t0, lane);
+                flush_full<P, RSV, TR, RTC>(st, k.out_a, io_o, rows, t0, lane);
             } else {
-                flush_tile<P, RSV>(st + 32 * RSV, k.out_t, row_out, b0, rows, t0, tl, lane);
+                flush_tile<P, RSV>(st + TR * RSV, k.out_t, row_out, b0, rows, t0, tl, lane);
                 flush_tile<P, RSV>(st, k.out_a, row_out, b0, rows, t0, tl, lane);
             }
             __syncwarp();
@@ -269,29 +283,46 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
 
 namespace {
 
-constexpr int NSTAGE = B200RL_NSTAGE;
+constexpr int NSTAGE = B200RL_NSTAGE;  // ring depth when the grid fills the machine
 
-template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
-int launch_rows(const ScanParams& k, cudaStream_t st) {
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int TR, int RTC>
+int launch_shape(const ScanParams& k, cudaStream_t st) {
     constexpr int RSV = RTC * P + 4;
     constexpr int RSR = RTC * (RHO_PP ? P : 1) + 4;
-    constexpr int STAGE = 32 * (2 * RSV + (NEED_RHO ? 2 * RSR : 0));
-    constexpr size_t SMEM = (size_t)NSTAGE * STAGE * sizeof(float);
-    auto kern = k_target_rows<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, NSTAGE>;
-    static int per_sm = 0;  // resident warps per SM for this instantiation
+    const bool alias = NEED_RHO && k.c.p == k.rho.p && k.c.sb == k.rho.sb && k.c.st == k.rho.st && k.c.sp == k.rho.sp;
+    const int stage = TR * (2 * RSV + (NEED_RHO ? (alias ? RSR : 2 * RSR) : 0));
+    auto kern = k_target_rows<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, TR, RTC>;
+    static int sms = 0;
+    static int per_sm_tab[2][3] = {};  // resident warps per SM of this instantiation by [c aliases rho][ns - 2]
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        constexpr size_t SMEM_MAX = (size_t)4 * TR * (2 * RSV + 2 * RSR) * sizeof(float);
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+    }
+    const int ntiles = (k.B + TR - 1) / TR;
+    // deepen the ring while all tiles still fit on the SMs at once (small B: latency-bound per warp)
+    const int want = (ntiles + sms - 1) / sms;
+    int ns = NSTAGE;
+    while (ns < 4 && (size_t)want * (ns + 1) * stage * sizeof(float) <= (size_t)200 * 1024) ++ns;
+    const size_t SMEM = (size_t)ns * stage * sizeof(float);
+    int& per_sm = per_sm_tab[alias ? 1 : 0][ns - 2];
     if (per_sm == 0) {
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
         int n = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, 32, SMEM) != cudaSuccess || n < 1) n = 1;
         per_sm = n;
     }
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int ntiles = (k.B + 31) / 32;
     const int grid = min(ntiles, sms * per_sm);
-    kern<<<grid, 32, SMEM, st>>>(k, ntiles);
+    kern<<<grid, 32, SMEM, st>>>(k, ntiles, alias ? 1 : 0, ns);
     return b200rl_check_launch("k_target_rows");
+}
+
+// long rows: 16-row tiles, 256 B per row per fetch (32 steps at P = 2, 64 at P = 1); rows of <= 64 steps: 32 x 16
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
+int launch_rows(const ScanParams& k, cudaStream_t st) {
+    if (k.T > B200RL_SHORT_T) return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 16, 64 / P>(k, st);
+    return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 32, 16>(k, st);
 }
 
 template <int MT, int MA, int P>

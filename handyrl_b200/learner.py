@@ -142,6 +142,7 @@ def compute_loss(batch, model, hidden, args, fused=True):
     fused = fused and outputs['policy'].is_cuda and outputs['policy'].dtype == torch.float32
     if fused:
         logp_t, clipped_rhos, cs = _PolicyTerms.apply(outputs['policy'], batch['policy'], actions, emask)
+        cs = clipped_rhos   # both thresholds are 1.0 (train.py:222): one tensor, the scan reads it once
     else:
         logp_b = F.log_softmax(batch['policy'], dim=-1).gather(-1, actions) * emask
         logp_t = F.log_softmax(outputs['policy'], dim=-1).gather(-1, actions) * emask

@@ -72,6 +72,25 @@ def test_fused_pair_equals_two_calls(vt, pt):
     assert torch.equal(tf, t1) and torch.equal(af, a2)
 
 
+@pytest.mark.parametrize("B,T,P,rpp", [(4096, 32, 2, False), (4096, 32, 2, True), (333, 64, 1, False), (65, 33, 4, False)])
+@pytest.mark.parametrize("vt,pt", [('VTRACE', 'UPGO'), ('VTRACE', 'VTRACE'), ('TD', 'VTRACE')])
+def test_cs_is_rhos_same_tensor(B, T, P, rpp, vt, pt):
+    """compute_loss passes one tensor for rhos and cs (both clipped at 1.0, train.py:222): the row kernel then
+    stages it once.  Results must equal the two-tensor call bit for bit, and the oracle."""
+    from handyrl_b200.losses import compute_target_pair
+    d = target_inputs(B, T, P, 'return', rpp, seed=B + T + 1)
+    d['cs'] = d['rhos'].copy()
+    rt, _ = targets_np.compute_target(vt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['cs'])
+    _, ra = targets_np.compute_target(pt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['cs'])
+    g = _cuda(d)
+    a = (g['values'], g['returns'], g['rewards'], g['lmb'], g['gamma'])
+    t2, a2 = compute_target_pair(vt, pt, *a, g['rhos'], g['cs'])      # two buffers
+    t1, a1 = compute_target_pair(vt, pt, *a, g['rhos'], g['rhos'])    # one buffer, aliased
+    assert torch.equal(t1, t2) and torch.equal(a1, a2)
+    _close(t1, np.asarray(rt))
+    _close(a1, np.asarray(ra))
+
+
 def test_noncontiguous_and_broadcast_views():
     from handyrl_b200.losses import compute_target
     d = target_inputs(50, 20, 2, 'return', seed=9)

@@ -1,7 +1,8 @@
 """compute_target sweep (BASELINE.json configs[4]): T in {32,200,1024} x B in {4096,65536} x P=2,
 all four modes + the fused V-Trace/UPGO pair, return head (rewards given) and value head (rewards None).
 Prints one JSON object; run on the GPU box:  python tools/sweep_targets.py > gpurun_out/sweep.json
-B200RL_TARGET_GENERIC=1 forces the generic strided kernel (A/B against the row-per-thread fast path)."""
+B200RL_TARGET_GENERIC=1 forces the generic strided kernel (A/B against the row-per-thread fast path).
+SWEEP_ALIAS=1 passes ONE tensor as rhos and cs (what learner.compute_loss does): 2 B/element less for V-Trace."""
 import json
 import os
 import sys
@@ -21,6 +22,9 @@ except Exception:
 BYTES = {"MC": (12, 8), "TD": (16, 12), "UPGO": (16, 12), "VTRACE": (20, 16), "VTRACE+UPGO": (20, 16)}
 
 
+ALIAS = bool(os.environ.get("SWEEP_ALIAS"))
+
+
 def bench(fn, sets, iters):
     for i in range(3):
         fn(sets[i % len(sets)])
@@ -37,7 +41,7 @@ def bench(fn, sets, iters):
 def main():
     dev = torch.device("cuda")
     g = torch.Generator(device=dev).manual_seed(0)
-    out = {"peak_gbs": PEAK, "generic": bool(os.environ.get("B200RL_TARGET_GENERIC")), "rows": []}
+    out = {"peak_gbs": PEAK, "generic": bool(os.environ.get("B200RL_TARGET_GENERIC")), "cs_is_rhos": ALIAS, "rows": []}
     Ts = [int(x) for x in os.environ.get('SWEEP_T', '32,200,1024').split(',')]
     Bs = [int(x) for x in os.environ.get('SWEEP_B', '4096,65536').split(',')]
     for T in Ts:
@@ -52,7 +56,7 @@ def main():
                 ret = torch.randn(B, T, P, 1, device=dev, generator=g)
                 oc = torch.randint(-1, 2, (B, 1, P, 1), device=dev, generator=g).float()
                 rho = torch.exp(0.5 * torch.randn(B, T, 1, 1, device=dev, generator=g)).clamp(0, 1)
-                sets.append((v, rew, ret, oc, rho, rho.clone()))
+                sets.append((v, rew, ret, oc, rho, rho if ALIAS else rho.clone()))
             iters = 20 if n > 5e7 else 50
             for head in ("return", "value"):
                 for mode in ("MC", "TD", "UPGO", "VTRACE", "VTRACE+UPGO"):
@@ -66,7 +70,7 @@ def main():
                     else:
                         fn = lambda s, m=mode: compute_target(m, s[0], s[3], None, 0.7, 1.0, s[4], s[5])
                     ms = bench(fn, sets, iters)
-                    by = BYTES[mode][0 if head == "return" else 1]
+                    by = BYTES[mode][0 if head == "return" else 1] - (2 if ALIAS and "VTRACE" in mode else 0)
                     gbs = n * by / (ms * 1e-3) / 1e9
                     out["rows"].append({"T": T, "B": B, "P": P, "head": head, "mode": mode, "ms": round(ms, 4),
                                         "elements_per_s": n / (ms * 1e-3), "bytes_per_element": by,
