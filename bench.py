@@ -311,10 +311,13 @@ def main():
         torch.cuda.synchronize()
         index = HostReplayIndex(gen, max_new_rows=1 << 15, n_threads=max(1, min(8, (os.cpu_count() or 1) // world)))
         win_pin = [torch.empty(B, 8, dtype=torch.int32).pin_memory() for _ in range(2)]
-        win_dev = torch.empty(B, 8, dtype=torch.int32, device=dev)
+        win_devs = [torch.empty(B, 8, dtype=torch.int32, device=dev) for _ in range(2)]
+        copy_stream = torch.cuda.Stream(device=dev)      # PCIe traffic runs beside the kernels, ordered by events
+        ev_roll = torch.cuda.Event()
+        ev_h2d = [torch.cuda.Event() for _ in range(2)]
         met_pin = torch.zeros(4, dtype=torch.float32).pin_memory()
         ev_done = torch.cuda.Event()
-        hs = {"win": None, "slot": 0, "pending": False, "metric": 0.0, "d2h": 0}
+        hs = {"win": None, "h2d": None, "slot": 0, "pending": False, "metric": 0.0, "d2h": 0}
 
         def step_tail(k, win):
             state["batch"] = batch = make_batch_windows(gen.store, win, TRAIN_ARGS, out=state["batch"])
@@ -323,30 +326,61 @@ def main():
             t2 = compute_target_pair("UPGO", "VTRACE", vr, batch["return"], batch["reward"], 0.7, 0.8, rho, c)
             return t1, t2
 
+        e2e_evs = []
+        tr_acc = {"enqueue_rollout": 0.0, "wait_prev_result": 0.0, "enqueue_tail": 0.0, "wait_fetch": 0.0,
+                  "host_select": 0.0}
+        pc = time.perf_counter
+
         def e2e_step(k):
+            t_a = pc()
+            evk = [ev() for _ in range(6)]
+            e2e_evs.append(evk)
+            evk[0].record()
             gen.rollout(PLIES, waves=waves, out_action=act_w)                   # async
-            index.fetch_async()                                                 # D2H: counters + new episode rows
+            evk[1].record()
+            ev_roll.record()
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(ev_roll)
+                index.fetch_async()                                             # D2H: counters + new episode rows
+            evk[2].record()
+            t_b = pc()
             if hs["pending"]:                                                   # D2H result of the previous step
                 ev_done.synchronize()
                 hs["metric"] = float(met_pin[0])
                 hs["pending"] = False
+            t_c = pc()
             if hs["win"] is not None:
-                win_dev.copy_(hs["win"], non_blocking=True)                     # H2D: windows drawn last iteration
-                (tv, av), (tr, ar) = step_tail(k, win_dev)
+                torch.cuda.current_stream().wait_event(hs["h2d"])               # H2D of these windows (copy stream)
+                evk[3].record()
+                (tv, av), (tr, ar) = step_tail(k, hs["win"])
+                evk[4].record()
                 met_pin.copy_(torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()]), non_blocking=True)
+                evk[5].record()
                 ev_done.record()
                 hs["pending"] = True
+            t_d = pc()
             # ---- host work, overlapped with the GPU: index the new episodes, draw the next windows ----
             index.commit()
+            t_e = pc()
             hs["d2h"] = index.d2h_bytes
-            buf = win_pin[hs["slot"]]
+            slot = hs["slot"]
             hs["slot"] ^= 1
-            hs["win"] = index.select(B, TRAIN_ARGS, buf, seed=rank)
+            buf = index.select(B, TRAIN_ARGS, win_pin[slot], seed=rank)
+            with torch.cuda.stream(copy_stream):                                # H2D: windows for the next step
+                win_devs[slot].copy_(buf, non_blocking=True)
+                ev_h2d[slot].record()
+            hs["win"], hs["h2d"] = win_devs[slot], ev_h2d[slot]
+            t_f = pc()
+            for name, dt_ in zip(tr_acc, (t_b - t_a, t_c - t_b, t_d - t_c, t_e - t_d, t_f - t_e)):
+                tr_acc[name] += dt_
 
         for k in range(4):
             e2e_step(k)
         barrier()
         ksteps = max(5, min(args.steps, 20))
+        for name in tr_acc:
+            tr_acc[name] = 0.0
+        e2e_evs.clear()
         t0 = time.perf_counter()
         for k in range(ksteps):
             e2e_step(k)
@@ -359,12 +393,16 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt.item())
         e2e = {"value": N_GAMES * PLIES * ksteps * world / dt, "unit": "env-steps/s",
-               "h2d_bytes_per_step": int(win_dev.numel() * 4),
+               "h2d_bytes_per_step": int(win_devs[0].numel() * 4),
                "d2h_bytes_per_step": int(hs["d2h"] + met_pin.numel() * 4),
                "steps": ksteps, "ms_per_step": dt / ksteps * 1e3,
+               "host_ms_per_step": {name: round(v_ / ksteps * 1e3, 4) for name, v_ in tr_acc.items()},
+               "gpu_ms_per_step": {name: round(sum(e_[i].elapsed_time(e_[i + 1]) for e_ in e2e_evs) / len(e2e_evs), 4)
+                                   for i, name in enumerate(("rollout", "enqueue_gap", "wait_h2d_windows",
+                                                             "make_batch_targets", "summary_d2h"))},
                "note": "per step: BatchGenerator.rollout; D2H of the counters and the new finished-episode rows; "
                        "HostReplayIndex.select (b200rl_select_windows_host, replay index on the host) overlapped with the GPU; pinned H2D of the "
-                       "windows; make_batch_windows; compute_target_pair x2; D2H of the target summary. Moments stay in "
+                       "windows on a copy stream (event-ordered) beside the kernels; make_batch_windows; compute_target_pair x2; D2H of the target summary. Moments stay in "
                        "HBM (the trajectory ring is the replay buffer). Wall clock incl. all host work."}
 
         # the same self-play driven ply by ply from HOST buffers (reference Environment-style stepping: actions

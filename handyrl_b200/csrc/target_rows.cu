@@ -14,6 +14,8 @@
 // and a persistent grid-stride over tiles keeps the 148 SMs evenly loaded.
 //
 // Arithmetic is the same Rec<> code as the generic kernel: bit-identical to torch fp32.
+#include <type_traits>
+
 #include "target_common.cuh"
 
 namespace {
@@ -217,46 +219,44 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
                 float* pr = st + TR * RSV + lane * RSV;
                 const float* prho = st + 2 * TR * RSV + lane * RSR;
                 const float* pc = c_alias ? prho : prho + TR * RSR;
-                // software pipeline over the 4-timestep groups: the LDS.128 of group q-1 are issued before
-                // the dependent fp32 chain of group q (the in-place stores would otherwise pin them behind it)
-                float4 nv[P], nr[P], nrho[WR], nc[WR];
-                auto load_group = [&](int q) {
+                // Software pipeline over the 4-timestep groups with two register sets (ping-pong): the LDS.128 of
+                // group q-1 are issued before the dependent fp32 chain of group q, and no register is copied
+                // between iterations.  The group holding the bootstrap step t = T-1 is peeled off.
+                struct Grp { float4 v[P], r[P], rho[WR], c[WR]; };
+                auto load_group = [&](Grp& g, int q) {
 #pragma unroll
                     for (int u = 0; u < P; ++u) {
-                        nv[u] = *reinterpret_cast<const float4*>(pv + q * 4 * P + 4 * u);
-                        if (HAS_REW) nr[u] = *reinterpret_cast<const float4*>(pr + q * 4 * P + 4 * u);
+                        g.v[u] = *reinterpret_cast<const float4*>(pv + q * 4 * P + 4 * u);
+                        if (HAS_REW) g.r[u] = *reinterpret_cast<const float4*>(pr + q * 4 * P + 4 * u);
                     }
                     if (NEED_RHO) {
 #pragma unroll
                         for (int u = 0; u < WR; ++u) {
-                            nrho[u] = *reinterpret_cast<const float4*>(prho + q * 4 * WR + 4 * u);
-                            nc[u] = *reinterpret_cast<const float4*>(pc + q * 4 * WR + 4 * u);
+                            g.rho[u] = *reinterpret_cast<const float4*>(prho + q * 4 * WR + 4 * u);
+                            if (!c_alias) g.c[u] = *reinterpret_cast<const float4*>(pc + q * 4 * WR + 4 * u);
                         }
                     }
                 };
-                load_group((tl >> 2) - 1);
-                for (int q = (tl >> 2) - 1; q >= 0; --q) {
+                auto compute_group = [&](const Grp& g, int q, auto first_tag) {
+                    constexpr bool FIRST = decltype(first_tag)::value;
                     float v[4 * P], rw[4 * P], rho[4 * WR], cc[4 * WR];
 #pragma unroll
                     for (int u = 0; u < P; ++u) {
-                        v[4 * u] = nv[u].x; v[4 * u + 1] = nv[u].y; v[4 * u + 2] = nv[u].z; v[4 * u + 3] = nv[u].w;
+                        v[4 * u] = g.v[u].x; v[4 * u + 1] = g.v[u].y; v[4 * u + 2] = g.v[u].z; v[4 * u + 3] = g.v[u].w;
                         if (HAS_REW) {
-                            rw[4 * u] = nr[u].x; rw[4 * u + 1] = nr[u].y; rw[4 * u + 2] = nr[u].z; rw[4 * u + 3] = nr[u].w;
+                            rw[4 * u] = g.r[u].x; rw[4 * u + 1] = g.r[u].y; rw[4 * u + 2] = g.r[u].z; rw[4 * u + 3] = g.r[u].w;
                         }
                     }
                     if (NEED_RHO) {
 #pragma unroll
                         for (int u = 0; u < WR; ++u) {
-                            rho[4 * u] = nrho[u].x; rho[4 * u + 1] = nrho[u].y; rho[4 * u + 2] = nrho[u].z; rho[4 * u + 3] = nrho[u].w;
-                            cc[4 * u] = nc[u].x; cc[4 * u + 1] = nc[u].y; cc[4 * u + 2] = nc[u].z; cc[4 * u + 3] = nc[u].w;
+                            rho[4 * u] = g.rho[u].x; rho[4 * u + 1] = g.rho[u].y; rho[4 * u + 2] = g.rho[u].z; rho[4 * u + 3] = g.rho[u].w;
+                            const float4 c4 = c_alias ? g.rho[u] : g.c[u];
+                            cc[4 * u] = c4.x; cc[4 * u + 1] = c4.y; cc[4 * u + 2] = c4.z; cc[4 * u + 3] = c4.w;
                         }
                     }
-                    if (q > 0) load_group(q - 1);
                     float tg[4 * P], ad[4 * P];
-                    if (t0 + q * 4 + 3 == k.T - 1)   // warp-uniform: the very first group holds the bootstrap step
-                        scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, true>(v, rw, rho, cc, rec_t, rec_a, R, k, tg, ad);
-                    else
-                        scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, false>(v, rw, rho, cc, rec_t, rec_a, R, k, tg, ad);
+                    scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, FIRST>(v, rw, rho, cc, rec_t, rec_a, R, k, tg, ad);
 #pragma unroll
                     for (int u = 0; u < P; ++u) {
                         *reinterpret_cast<float4*>(pv + q * 4 * P + 4 * u) =
@@ -264,7 +264,23 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
                         *reinterpret_cast<float4*>(pr + q * 4 * P + 4 * u) =
                             make_float4(tg[4 * u], tg[4 * u + 1], tg[4 * u + 2], tg[4 * u + 3]);
                     }
+                };
+                Grp ga, gb;
+                int q = (tl >> 2) - 1;
+                load_group(ga, q);
+                if (ch == nchunks - 1) {   // warp-uniform: this chunk starts with the bootstrap step
+                    if (q >= 1) load_group(gb, q - 1);
+                    compute_group(ga, q, std::true_type{});
+                    --q;
+                    if (q >= 0) ga = gb;
                 }
+                for (; q >= 1; q -= 2) {
+                    load_group(gb, q - 1);
+                    compute_group(ga, q, std::false_type{});
+                    if (q >= 2) load_group(ga, q - 2);
+                    compute_group(gb, q - 1, std::false_type{});
+                }
+                if (q == 0) compute_group(ga, 0, std::false_type{});
             }
             __syncwarp();
             if (tl == RTC) {
