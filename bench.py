@@ -463,7 +463,7 @@ def main():
                             "env-step"),
             "make_batch": roof("k_select_windows + k_make_batch<Geister>", BYTES_PER_BATCH_CELL * B * T, batch_ms,
                                BYTES_PER_BATCH_CELL, "(b,t) batch cell"),
-            "targets": roof("k_target_scan<UPGO,VTRACE> x2 (value + return head)", BYTES_PER_TARGET_PAIR * B * T * P,
+            "targets": roof("k_target_rows<UPGO,VTRACE> x2 (value + return head)", BYTES_PER_TARGET_PAIR * B * T * P,
                             tgt_ms, BYTES_PER_TARGET_PAIR, "(b,t,p) element, both heads"),
         }
         dominant = max(roofs, key=lambda k: roofs[k]["avg_ms"])

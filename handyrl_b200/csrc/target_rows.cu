@@ -14,6 +14,7 @@
 // and a persistent grid-stride over tiles keeps the 148 SMs evenly loaded.
 //
 // Arithmetic is the same Rec<> code as the generic kernel: bit-identical to torch fp32.
+#include <cstdlib>
 #include <type_traits>
 
 #include "target_common.cuh"
@@ -329,7 +330,12 @@ int launch_shape(const ScanParams& k, cudaStream_t st) {
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, 32, SMEM) != cudaSuccess || n < 1) n = 1;
         per_sm = n;
     }
-    const int grid = min(ntiles, sms * per_sm);
+    // One CTA (= one warp) per tile, dispatched by the hardware as slots free up: SMs differ by up to 2x in the
+    // HBM bandwidth they can draw (tools/probe_write4.cu), so a static tile stride runs at the pace of the slowest
+    // SM (6.3 TB/s for a pure write stream) while dynamic dispatch reaches 7.3.  B200RL_TARGET_PERSISTENT=1
+    // restores the persistent grid-stride launch for A/B measurements.
+    static const bool persistent = getenv("B200RL_TARGET_PERSISTENT") != nullptr;
+    const int grid = persistent ? min(ntiles, sms * per_sm) : ntiles;
     kern<<<grid, 32, SMEM, st>>>(k, ntiles, alias ? 1 : 0, ns);
     return b200rl_check_launch("k_target_rows");
 }
