@@ -238,7 +238,7 @@ struct RolloutParams {
     float* out_amask;   // [waves][N][A] or null
     int32_t* out_action;  // [waves][N] or null
     int64_t waves;
-    uint4* traj;        // [D][N] 32-byte compact records or null
+    uint4* traj;        // [N][D] 32-byte compact records (slot-major ring) or null
     int64_t D;
     int32_t* ep_table;  // [E][4] = slot, steps | win << 16, end_it lo, end_it hi
     int64_t E;
@@ -252,10 +252,14 @@ struct RolloutParams {
 template <class G>
 __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
     __shared__ CtaStage<G> stage;
+    // write combining of the trajectory records: 4 plies x 32 B per game = one 128-byte line of the slot-major
+    // ring, staged as [ply & 3][half][lane] 16-byte units (conflict-free) and flushed every 4th ply
+    __shared__ uint4 rec_stage[WARPS][4][2][32];
     stage.init();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t g0 = (blockIdx.x * (int64_t)WARPS + warp) * 32;
     if (g0 >= p.N) return;
+    uint32_t rec_fill = 0;   // bit q: rec_stage[..][q] holds the record of the current 4-ply group
     const int ng = (int)min((int64_t)32, p.N - g0);
     const bool valid = lane < ng;
     const int64_t i = g0 + lane;
@@ -306,7 +310,9 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                          ((term ? 1u : 0u) << 25) | (wincode << 26);
                 rec[6] = (uint32_t)G::steps(s);
                 rec[7] = 0;
-                st_record(p.traj, p.D, p.N, it, i, rec);
+                const int q = (int)(it & 3);
+                rec_stage[warp][q][0][lane] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
+                rec_stage[warp][q][1][lane] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
             }
             if (term) {
                 n_ep += 1;
@@ -321,6 +327,28 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                     e[2] = (int32_t)(uint32_t)it;
                     e[3] = (int32_t)(uint32_t)(it >> 32);
                 }
+            }
+        }
+        if (p.traj) {
+            // flush the 4-ply group, transposed: lanes 8q..8q+7 carry ply q of 8 consecutive games, so every
+            // game's (up to) 128-byte line leaves the SM as one request of full 32-byte sectors
+            rec_fill |= 1u << (int)(it & 3);
+            if ((it & 3) == 3 || k == p.n_plies - 1) {
+                __syncwarp();
+                const int q = lane >> 3;
+                if (rec_fill & (1u << q)) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int gq = 8 * j + (lane & 7);
+                        if (gq < ng) {
+                            const uint4 lo = rec_stage[warp][q][0][gq], hi = rec_stage[warp][q][1][gq];
+                            const uint32_t r8[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+                            st_record(p.traj, p.D, p.N, (it & ~(uint64_t)3) + (uint64_t)q, g0 + gq, r8);
+                        }
+                    }
+                }
+                rec_fill = 0;
+                __syncwarp();
             }
         }
     }

@@ -166,7 +166,7 @@ class BatchedEnv:
             main, scalar, am = waves.get("main"), waves.get("scalar"), waves.get("action_mask")
             ref = main if main is not None else am
             W = ref.shape[0]
-        D = 0 if traj is None else traj.shape[0]
+        D = 0 if traj is None else traj.shape[1]     # (N, D, 8) slot-major ring
         E = 0 if ep_table is None else ep_table.shape[0]
         with torch.cuda.device(self.device):
             _lib.call("b200rl_env_rollout", self.game, self._st(), self.N, int(n_plies), int(seed),

@@ -20,7 +20,7 @@ from .engine import BatchedEnv, _ptr
 
 
 class TrajectoryStore:
-    """Ring of per-ply records for N game slots: [D][N] x 32 B (32 B per ply and slot),
+    """Ring of per-ply records for N game slots: [N][D] x 32 B, slot-major (the plies of a window are contiguous),
     plus the finished-episode table and counters filled by the kernels."""
 
     def __init__(self, env, depth=None, max_episodes=1 << 16, record_values=False, record_logits=False):
@@ -28,7 +28,7 @@ class TrajectoryStore:
         self.N = env.N
         self.D = int(depth or max(2 * env.max_steps + 64, 64))
         dev = env.device
-        self.traj = torch.zeros(self.D, self.N, 8, dtype=torch.int32, device=dev)
+        self.traj = torch.zeros(self.N, self.D, 8, dtype=torch.int32, device=dev)
         self.E = int(max_episodes)
         self.ep_table = torch.zeros(self.E, 4, dtype=torch.int32, device=dev)
         self.counters = torch.zeros(8, dtype=torch.int64, device=dev)

@@ -148,7 +148,8 @@ int b200rl_env_step_observe(int game, void* state, int64_t N, const int32_t* act
  *   seed, game_id_base, it0 : counter-RNG key (seed, game_id_base + slot, it0 + ply)
  *   out_main/out_scalar/out_amask/out_action : moment data of ply `it`, written to wave
  *       (it % waves) of [waves][N][...] buffers; any may be NULL
- *   traj : [D][N] ring of 32-byte compact records (8 x uint32, 32-byte aligned), or NULL
+ *   traj : [N][D] slot-major ring of 32-byte compact records (8 x uint32, 32-byte aligned): record of
+ *          (iteration it, slot i) at (i * D + it % D) * 32 bytes, or NULL
  *   ep_table : (E, 4) int32 ring of finished episodes {slot, steps | win << 16, end_it lo, hi}
  *   counters : uint64[8] {episodes, env steps, player0 wins, player1 wins, draws, ep_table cursor, -, -}
  */
@@ -193,7 +194,7 @@ enum { B200RL_BATCH_TURN = 0, B200RL_BATCH_ALL = 1, B200RL_BATCH_SOLO = 2 };
 /*
  * make_batch(episodes, args) (handyrl/train.py:33-133) over windows of the device
  * trajectory ring.
- *   traj     : [D][N] x 32 B ring written by b200rl_env_rollout / b200rl_env_step_record
+ *   traj     : [N][D] x 32 B slot-major ring written by b200rl_env_rollout / b200rl_env_step_record
  *   values   : [D][N][2] fp32 value estimates recorded beside the ring, or NULL (RandomModel: 0)
  *   logits   : [D][N][A] fp32 behaviour logits, or NULL (RandomModel: zero logits)
  *   windows  : (B,8) int32 {slot, first_it lo, first_it hi, len = end-start, start, total steps,

@@ -46,7 +46,7 @@ def test_parallel_tictactoe_samples_both_players():
     u = torch.rand(N, 2, dtype=torch.float64, device='cuda')
     act, term = gen.act(logits, u=u)
     assert act.shape == (N, 2) and int(act.min()) >= 0 and int(act.max()) < 9
-    rec = gen.store.traj[0, :, 4:].cpu().numpy().view(np.uint32)   # words 4..7 of the records of iteration 0
+    rec = gen.store.traj[:, 0, 4:].cpu().numpy().view(np.uint32)   # words 4..7 of the records of iteration 0
     landed, sel = rec[:, 1] & 0xFFFF, (rec[:, 1] >> 16) & 1
     a = act.cpu().numpy()
     assert np.array_equal(landed, a[np.arange(N), sel])

@@ -18,14 +18,15 @@ def _rollout(env_key, N, K, chunks=1, seed=7):
     main, scalar = env.alloc_obs(waves=K)
     waves = dict(main=main, scalar=scalar, action_mask=torch.empty(K, N, env.A, device='cuda'))
     act = torch.full((K, N), -9, dtype=torch.int32, device='cuda')
-    traj = torch.zeros(K, N, 8, dtype=torch.int32, device='cuda')
+    traj = torch.zeros(N, K, 8, dtype=torch.int32, device='cuda')     # slot-major ring [N][D]
     ept = torch.zeros(4 * N * K // 2 + 16, 4, dtype=torch.int32, device='cuda')
     ctr = torch.zeros(8, dtype=torch.int64, device='cuda')
     per = K // chunks
     for c in range(chunks):
         env.rollout(per, seed=seed, waves=waves, traj=traj, ep_table=ept, counters=ctr, out_action=act)
     torch.cuda.synchronize()
-    return env, waves, act.cpu().numpy(), traj.cpu().numpy(), ept.cpu().numpy(), ctr.cpu().numpy()
+    # tests index the records as [ply][game]
+    return env, waves, act.cpu().numpy(), traj.cpu().numpy().transpose(1, 0, 2).copy(), ept.cpu().numpy(), ctr.cpu().numpy()
 
 
 @pytest.mark.parametrize("env_key,N,K", [('tictactoe', 96, 64), ('parallel_tictactoe', 96, 64), ('geister', 70, 420),
@@ -87,6 +88,12 @@ def test_rollout_is_chunk_invariant_and_seeded():
     assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
     assert not np.array_equal(a[2], c[2])
     assert torch.equal(a[0].state, b[0].state)
+    # launches that start and end inside a 4-ply record group (the rollout combines 4 records per 128-byte line)
+    d = _rollout('geister', 64, 126, chunks=1, seed=3)
+    e = _rollout('geister', 64, 126, chunks=6, seed=3)      # 21 plies per launch
+    f = _rollout('geister', 64, 126, chunks=126, seed=3)    # one ply per launch
+    assert np.array_equal(d[3], e[3]) and np.array_equal(d[3], f[3]) and np.array_equal(d[2], f[2])
+    assert np.array_equal(d[3], a[3][:126])
 
 
 def test_uniform_policy_statistics():
