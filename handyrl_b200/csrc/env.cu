@@ -3,6 +3,10 @@
 // Replaces, for N concurrent games, the per-game Python calls of the reference
 // `Environment` interface (handyrl/environment.py:43-146) and the body of the
 // self-play loop that drives it (handyrl/generation.py:31-68).
+#include <cstdlib>
+#include <map>
+#include <mutex>
+
 #include "common.cuh"
 #include "games.cuh"
 #include "emit.cuh"
@@ -243,12 +247,32 @@ struct RolloutParams {
     int32_t* ep_table;  // [E][4] = slot, steps | win << 16, end_it lo, end_it hi
     int64_t E;
     unsigned long long* counters;  // [0] episodes, [1] env steps, [2] BLACK wins, [3] WHITE wins, [4] draws
+    unsigned int* sched;   // [0] ticket counter, [SCHED_HDR + g] chunks completed for game group g (zeroed per launch)
+    int64_t chunk;         // plies per ticket
 };
+constexpr int SCHED_HDR = 32;
+
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
 // Persistent self-play with the epoch-0 policy (uniform over legal actions ==
-// RandomModel's zero logits, handyrl/model.py:58-64): state stays in registers for
-// n_plies plies; every ply emits the reference-format moment data (observation,
-// action_mask, action) and/or a 32-byte compact trajectory record.
+// RandomModel's zero logits, handyrl/model.py:58-64): every ply emits the reference-format moment data
+// (observation, action_mask, action) and/or a 32-byte compact trajectory record.
+//
+// Work is handed out as TICKETS (group of 32 games, chunk of `chunk` plies) from a global counter: ticket
+// t = chunk c of group g = t % ngroups.  Within a ticket the 32 game states live in registers; between the
+// chunks of a group they go through global memory (64 B per game) and a per-group progress word
+// (release/acquire).  Why: the SMs of a B200 differ by up to 2x in the HBM bandwidth they can draw
+// (tools/probe_write4.cu), so a static games->warp assignment finishes at the pace of the slowest SM (a pure
+// write stream: 6.3 TB/s static, 7.2 TB/s with dynamic assignment); with tickets the fast SMs take more chunks.
+// A ticket only ever waits for a ticket that a RUNNING warp claimed earlier, so there is no deadlock whatever
+// the number of resident CTAs.  Results depend on (game, iteration) only, not on which warp ran a ticket.
 template <class G>
 __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
     __shared__ CtaStage<G> stage;
@@ -257,102 +281,131 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
     __shared__ uint4 rec_stage[WARPS][4][2][32];
     stage.init();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t g0 = (blockIdx.x * (int64_t)WARPS + warp) * 32;
-    if (g0 >= p.N) return;
-    uint32_t rec_fill = 0;   // bit q: rec_stage[..][q] holds the record of the current 4-ply group
-    const int ng = (int)min((int64_t)32, p.N - g0);
-    const bool valid = lane < ng;
-    const int64_t i = g0 + lane;
-    typename G::State s;
-    G::reset(s);
-    if (valid) s = G::load(p.state, p.N, i);
+    const int64_t ngroups = (p.N + 31) / 32;
+    const int64_t nchunks = (p.n_plies + p.chunk - 1) / p.chunk;
+    const int64_t ntickets = ngroups * nchunks;
     unsigned int n_ep = 0, n_w0 = 0, n_w1 = 0, n_dr = 0;
-    const uint64_t stream_id = p.game_id_base + (uint64_t)i;
+    unsigned long long n_steps = 0;
+    uint32_t rec_fill = 0;   // bit q: rec_stage[..][q] holds the record of the current 4-ply group
 
-    for (int64_t k = 0; k < p.n_plies; ++k) {
-        const uint64_t it = p.it0 + (uint64_t)k;
-        bool first = false;
-        if (valid && G::terminal(s)) G::reset(s);  // auto-reset: a finished slot starts its next episode
-        if (valid) first = G::steps(s) == 0;
-        // policy: uniform over the legal actions
-        uint32_t lm[G::LW];
-#pragma unroll
-        for (int w = 0; w < G::LW; ++w) lm[w] = 0;
-        int action = -1, selp = 0;
-        if (valid) {
-            G::legal_bits(s, lm);
-            int cnt = 0;
-#pragma unroll
-            for (int w = 0; w < G::LW; ++w) cnt += __popc(lm[w]);
-            const uint32_t r = b200rl_rand32(p.seed, stream_id, it);
-            const int kk = (int)__umulhi(r, (uint32_t)cnt);
-            action = kth_set_bit<G::LW>(lm, kk);
-            selp = (int)((r >> 7) & 1);  // ParallelTicTacToe: which player's move lands
-        }
-        const int64_t wv = p.waves > 0 ? (int64_t)(it % (uint64_t)p.waves) : 0;
-        if (p.out_main || p.out_amask || p.out_scalar) {
-            emit_views<G>(stage, warp, s, valid, B200RL_VIEW_TURN, g0, ng, lane,
-                          p.out_main ? p.out_main + wv * p.N * G::OBITS : nullptr,
-                          p.out_scalar ? p.out_scalar + wv * p.N * G::SBITS : nullptr,
-                          p.out_amask ? p.out_amask + wv * p.N * G::A : nullptr, nullptr);
-        }
-        if (valid) {
-            if (p.out_action) p.out_action[wv * p.N + i] = action;
-            uint32_t rec[8];
-            if (p.traj) G::pack_record(s, rec);
-            G::step(s, action, selp);
-            const bool term = G::terminal(s);
-            float o0 = 0.f, o1 = 0.f;
-            if (term) G::outcome(s, o0, o1);
-            const uint32_t wincode = term ? (o0 > 0 ? 1u : (o1 > 0 ? 2u : 3u)) : 0u;
-            if (p.traj) {
-                rec[5] = ((uint32_t)action & 0xFFFF) | ((uint32_t)selp << 16) | ((first ? 1u : 0u) << 24) |
-                         ((term ? 1u : 0u) << 25) | (wincode << 26);
-                rec[6] = (uint32_t)G::steps(s);
-                rec[7] = 0;
-                const int q = (int)(it & 3);
-                rec_stage[warp][q][0][lane] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
-                rec_stage[warp][q][1][lane] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
-            }
-            if (term) {
-                n_ep += 1;
-                n_w0 += wincode == 1;
-                n_w1 += wincode == 2;
-                n_dr += wincode == 3;
-                if (p.ep_table) {
-                    unsigned long long idx = atomicAdd(&p.counters[5], 1ull);
-                    int32_t* e = p.ep_table + (int64_t)(idx % (unsigned long long)p.E) * 4;
-                    e[0] = (int32_t)i;
-                    e[1] = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
-                    e[2] = (int32_t)(uint32_t)it;
-                    e[3] = (int32_t)(uint32_t)(it >> 32);
+    for (;;) {
+        unsigned int tk = 0;
+        if (lane == 0) tk = atomicAdd(&p.sched[0], 1u);
+        tk = __shfl_sync(0xffffffffu, tk, 0);
+        if ((int64_t)tk >= ntickets) break;
+        const int64_t ch = (int64_t)tk / ngroups, grp = (int64_t)tk - ch * ngroups;
+        const int64_t g0 = grp * 32;
+        const int ng = (int)min((int64_t)32, p.N - g0);
+        const bool valid = lane < ng;
+        const int64_t i = g0 + lane;
+        if (ch > 0) {   // the previous chunk of this group must have stored its states
+            if (lane == 0) {
+                unsigned int spins = 0;
+                while (ld_acquire_u32(p.sched + SCHED_HDR + grp) < (unsigned int)ch) {
+                    __nanosleep(100);
+                    if (++spins > (1u << 24)) break;   // ~2 s: never hang the GPU on a scheduling bug
                 }
             }
+            __syncwarp();
+            __threadfence();
         }
-        if (p.traj) {
-            // flush the 4-ply group, transposed: lanes 8q..8q+7 carry ply q of 8 consecutive games, so every
-            // game's (up to) 128-byte line leaves the SM as one request of full 32-byte sectors
-            rec_fill |= 1u << (int)(it & 3);
-            if ((it & 3) == 3 || k == p.n_plies - 1) {
-                __syncwarp();
-                const int q = lane >> 3;
-                if (rec_fill & (1u << q)) {
+        typename G::State s;
+        G::reset(s);
+        if (valid) s = G::load_cg(p.state, p.N, i);
+        const uint64_t stream_id = p.game_id_base + (uint64_t)i;
+        const int64_t k_begin = ch * p.chunk, k_end = min(k_begin + p.chunk, p.n_plies);
+
+        for (int64_t k = k_begin; k < k_end; ++k) {
+            const uint64_t it = p.it0 + (uint64_t)k;
+            bool first = false;
+            if (valid && G::terminal(s)) G::reset(s);  // auto-reset: a finished slot starts its next episode
+            if (valid) first = G::steps(s) == 0;
+            // policy: uniform over the legal actions
+            uint32_t lm[G::LW];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int gq = 8 * j + (lane & 7);
-                        if (gq < ng) {
-                            const uint4 lo = rec_stage[warp][q][0][gq], hi = rec_stage[warp][q][1][gq];
-                            const uint32_t r8[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-                            st_record(p.traj, p.D, p.N, (it & ~(uint64_t)3) + (uint64_t)q, g0 + gq, r8);
-                        }
+            for (int w = 0; w < G::LW; ++w) lm[w] = 0;
+            int action = -1, selp = 0;
+            if (valid) {
+                G::legal_bits(s, lm);
+                int cnt = 0;
+#pragma unroll
+                for (int w = 0; w < G::LW; ++w) cnt += __popc(lm[w]);
+                const uint32_t r = b200rl_rand32(p.seed, stream_id, it);
+                const int kk = (int)__umulhi(r, (uint32_t)cnt);
+                action = kth_set_bit<G::LW>(lm, kk);
+                selp = (int)((r >> 7) & 1);  // ParallelTicTacToe: which player's move lands
+            }
+            const int64_t wv = p.waves > 0 ? (int64_t)(it % (uint64_t)p.waves) : 0;
+            if (p.out_main || p.out_amask || p.out_scalar) {
+                emit_views<G>(stage, warp, s, valid, B200RL_VIEW_TURN, g0, ng, lane,
+                              p.out_main ? p.out_main + wv * p.N * G::OBITS : nullptr,
+                              p.out_scalar ? p.out_scalar + wv * p.N * G::SBITS : nullptr,
+                              p.out_amask ? p.out_amask + wv * p.N * G::A : nullptr, nullptr);
+            }
+            if (valid) {
+                if (p.out_action) p.out_action[wv * p.N + i] = action;
+                uint32_t rec[8];
+                if (p.traj) G::pack_record(s, rec);
+                G::step(s, action, selp);
+                const bool term = G::terminal(s);
+                float o0 = 0.f, o1 = 0.f;
+                if (term) G::outcome(s, o0, o1);
+                const uint32_t wincode = term ? (o0 > 0 ? 1u : (o1 > 0 ? 2u : 3u)) : 0u;
+                if (p.traj) {
+                    rec[5] = ((uint32_t)action & 0xFFFF) | ((uint32_t)selp << 16) | ((first ? 1u : 0u) << 24) |
+                             ((term ? 1u : 0u) << 25) | (wincode << 26);
+                    rec[6] = (uint32_t)G::steps(s);
+                    rec[7] = 0;
+                    const int q = (int)(it & 3);
+                    rec_stage[warp][q][0][lane] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
+                    rec_stage[warp][q][1][lane] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
+                }
+                if (term) {
+                    n_ep += 1;
+                    n_w0 += wincode == 1;
+                    n_w1 += wincode == 2;
+                    n_dr += wincode == 3;
+                    if (p.ep_table) {
+                        unsigned long long idx = atomicAdd(&p.counters[5], 1ull);
+                        int32_t* e = p.ep_table + (int64_t)(idx % (unsigned long long)p.E) * 4;
+                        e[0] = (int32_t)i;
+                        e[1] = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
+                        e[2] = (int32_t)(uint32_t)it;
+                        e[3] = (int32_t)(uint32_t)(it >> 32);
                     }
                 }
-                rec_fill = 0;
-                __syncwarp();
+            }
+            if (p.traj) {
+                // flush the 4-ply group, transposed: lanes 8q..8q+7 carry ply q of 8 consecutive games, so every
+                // game's (up to) 128-byte line leaves the SM as one request of full 32-byte sectors
+                rec_fill |= 1u << (int)(it & 3);
+                if ((it & 3) == 3 || k == k_end - 1) {
+                    __syncwarp();
+                    const int q = lane >> 3;
+                    if (rec_fill & (1u << q)) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int gq = 8 * j + (lane & 7);
+                            if (gq < ng) {
+                                const uint4 lo = rec_stage[warp][q][0][gq], hi = rec_stage[warp][q][1][gq];
+                                const uint32_t r8[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+                                st_record(p.traj, p.D, p.N, (it & ~(uint64_t)3) + (uint64_t)q, g0 + gq, r8);
+                            }
+                        }
+                    }
+                    rec_fill = 0;
+                    __syncwarp();
+                }
             }
         }
+        if (valid) G::store(p.state, p.N, i, s);
+        n_steps += (unsigned long long)ng * (unsigned long long)(k_end - k_begin);
+        if (nchunks > 1) {   // publish: states of this group are valid up to chunk ch
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) st_release_u32(p.sched + SCHED_HDR + grp, (unsigned int)(ch + 1));
+        }
     }
-    if (valid) G::store(p.state, p.N, i, s);
     if (p.counters) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -363,7 +416,7 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
         }
         if (lane == 0) {
             atomicAdd(&p.counters[0], (unsigned long long)n_ep);
-            atomicAdd(&p.counters[1], (unsigned long long)ng * (unsigned long long)p.n_plies);
+            atomicAdd(&p.counters[1], n_steps);
             atomicAdd(&p.counters[2], (unsigned long long)n_w0);
             atomicAdd(&p.counters[3], (unsigned long long)n_w1);
             atomicAdd(&p.counters[4], (unsigned long long)n_dr);
@@ -374,6 +427,27 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
 inline int grid_for(int64_t N) { return (int)((N + BLK - 1) / BLK); }
 
 }  // namespace
+
+// Ticket scratch of the rollout, one buffer per (device, stream), grown on demand and kept for the process.
+static unsigned int* rollout_sched(int dev, void* stream, size_t words) {
+    static std::mutex mu;
+    static std::map<std::pair<int, void*>, std::pair<unsigned int*, size_t>> bufs;
+    std::lock_guard<std::mutex> lock(mu);
+    auto& e = bufs[std::make_pair(dev, stream)];
+    if (e.second < words) {
+        if (e.first) cudaFree(e.first);
+        e.first = nullptr;
+        e.second = 0;
+        const size_t cap = words + words / 2 + 1024;
+        if (cudaMalloc(&e.first, cap * sizeof(unsigned int)) != cudaSuccess) {
+            cudaGetLastError();
+            e.first = nullptr;
+            return nullptr;
+        }
+        e.second = cap;
+    }
+    return e.first;
+}
 
 #define DISPATCH_GAME(game, EXPR)                                                       \
     switch (game) {                                                                     \
@@ -494,6 +568,24 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     p.it0 = it0; p.out_main = out_main; p.out_scalar = out_scalar; p.out_amask = out_amask;
     p.out_action = out_action; p.waves = waves; p.traj = (uint4*)traj; p.D = D; p.ep_table = ep_table; p.E = E;
     p.counters = (unsigned long long*)counters;
-    DISPATCH_GAME(game, (k_rollout<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(p)));
+    if (N <= 0 || n_plies <= 0) return B200RL_OK;
+    // tickets: 4-ply chunks (one 128-byte record line) once there are enough groups and plies to balance
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t ngroups = (N + 31) / 32;
+    static const char* chunk_env = getenv("B200RL_ROLLOUT_CHUNK");   // experiments: 0 = one chunk per group (static)
+    int64_t chunk = chunk_env ? atoll(chunk_env) : 4;
+    if (chunk <= 0 || n_plies < 2 * chunk || ngroups < 2 * sms) chunk = n_plies;
+    const int64_t nchunks = (n_plies + chunk - 1) / chunk;
+    B200RL_REQUIRE(ngroups * nchunks < (int64_t)0xFFFF0000u, "env_rollout: too many tickets (N * n_plies)");
+    unsigned int* sched = rollout_sched(dev, stream, (size_t)(SCHED_HDR + ngroups));
+    B200RL_REQUIRE(sched != nullptr, "env_rollout: cannot allocate the ticket scratch (first call inside a graph capture?)");
+    cudaMemsetAsync(sched, 0, (size_t)(SCHED_HDR + ngroups) * sizeof(unsigned int), (cudaStream_t)stream);
+    p.sched = sched;
+    p.chunk = chunk;
+    const int64_t want = (ngroups + WARPS - 1) / WARPS;
+    const int grid = (int)min(want, (int64_t)sms * 8);   // persistent: at most __launch_bounds__(BLK, 8) CTAs per SM
+    DISPATCH_GAME(game, (k_rollout<G><<<grid, BLK, 0, (cudaStream_t)stream>>>(p)));
     return b200rl_check_launch("k_rollout");
 }

@@ -41,6 +41,12 @@ struct TicTacToeGame {
         s.w = st[i];
         return s;
     }
+    // L2-coherent load: the state may have been written by another SM earlier in the same kernel (rollout tickets)
+    __device__ __forceinline__ static State load_cg(const uint32_t* st, int64_t N, int64_t i) {
+        State s;
+        s.w = __ldcg(st + i);
+        return s;
+    }
     __device__ __forceinline__ static void store(uint32_t* __restrict__ st, int64_t N, int64_t i, const State& s) {
         st[i] = s.w;
     }
@@ -156,6 +162,18 @@ struct GeisterGame {
     __device__ __forceinline__ static State load(const uint32_t* __restrict__ st, int64_t N, int64_t i) {
         const uint4* p = reinterpret_cast<const uint4*>(st);
         uint4 a = p[i], b = p[N + i], c = p[2 * N + i], d = p[3 * N + i];
+        State s;
+        s.bb[0] = a.x | ((uint64_t)a.y << 32);
+        s.bb[1] = a.z | ((uint64_t)a.w << 32);
+        s.bb[2] = b.x | ((uint64_t)b.y << 32);
+        s.bb[3] = b.z | ((uint64_t)b.w << 32);
+        s.pos[0] = c.x; s.pos[1] = c.y; s.pos[2] = c.z; s.pos[3] = c.w;
+        s.tc = d.x; s.win = d.y; s.aux = d.z; s.spare = d.w;
+        return s;
+    }
+    __device__ __forceinline__ static State load_cg(const uint32_t* st, int64_t N, int64_t i) {
+        const uint4* p = reinterpret_cast<const uint4*>(st);
+        uint4 a = __ldcg(p + i), b = __ldcg(p + N + i), c = __ldcg(p + 2 * N + i), d = __ldcg(p + 3 * N + i);
         State s;
         s.bb[0] = a.x | ((uint64_t)a.y << 32);
         s.bb[1] = a.z | ((uint64_t)a.w << 32);

@@ -152,6 +152,9 @@ int b200rl_env_step_observe(int game, void* state, int64_t N, const int32_t* act
  *          (iteration it, slot i) at (i * D + it % D) * 32 bytes, or NULL
  *   ep_table : (E, 4) int32 ring of finished episodes {slot, steps | win << 16, end_it lo, hi}
  *   counters : uint64[8] {episodes, env steps, player0 wins, player1 wins, draws, ep_table cursor, -, -}
+  * Scheduling: (32-game group, 4-ply chunk) tickets from a library-owned scratch buffer per (device, stream),
+ * allocated on first use (so the first call on a stream must not happen inside a CUDA-graph capture).
+ * Results depend on (game, iteration) only.  Env B200RL_ROLLOUT_CHUNK=0 disables chunking (A/B measurements).
  */
 int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_plies, uint64_t seed, uint64_t game_id_base,
                        uint64_t it0, float* out_main, float* out_scalar, float* out_amask, int32_t* out_action,
