@@ -575,7 +575,20 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int64_t ngroups = (N + 31) / 32;
     static const char* chunk_env = getenv("B200RL_ROLLOUT_CHUNK");   // experiments: 0 = one chunk per group (static)
-    int64_t chunk = chunk_env ? atoll(chunk_env) : 4;
+    int64_t chunk;
+    if (chunk_env) {
+        chunk = atoll(chunk_env);
+    } else {
+        // a ticket should move ~256 KB (Geister with full moments: 4 plies x 32 games x 1972 B) so that the ticket
+        // overhead (atomic, 64 B/game state round trip, fence) stays ~1 %; always a multiple of the 4-ply record line
+        int64_t dims[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (b200rl_env_dims(game, dims) != B200RL_OK) return B200RL_ERR_ARG;
+        const int64_t A = dims[0], obits = dims[1], sbits = dims[2];
+        const int64_t per_step = (out_main ? 4 * obits : 0) + (out_scalar ? 4 * sbits : 0) + (out_amask ? 4 * A : 0) +
+                                 (out_action ? 4 : 0) + (traj ? 32 : 0) + 8;
+        chunk = ((262144 / (32 * per_step)) + 3) / 4 * 4;
+        if (chunk < 4) chunk = 4;
+    }
     if (chunk <= 0 || n_plies < 2 * chunk || ngroups < 2 * sms) chunk = n_plies;
     const int64_t nchunks = (n_plies + chunk - 1) / chunk;
     B200RL_REQUIRE(ngroups * nchunks < (int64_t)0xFFFF0000u, "env_rollout: too many tickets (N * n_plies)");
