@@ -167,6 +167,9 @@ def cpu_baseline(seconds_target=12.0):
             "phase_share": {"generation": ph[0] / tot, "make_batch": ph[1] / tot, "targets": ph[2] / tot}}
 
 
+RESULT_OUT = sys.stdout
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference is pure Python and cannot travel to the GPU box (in the build container it
     runs ~5.4 k Geister plies/s/process); the timed arm is the C oracle port of the same step on
@@ -192,7 +195,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -210,6 +213,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    # stdout carries exactly ONE line (the JSON): library chatter written to fd 1 (NCCL prints its version banner
+    # there) goes to stderr, the result line to a private duplicate of the original stdout
+    global RESULT_OUT
+    sys.stdout.flush()
+    RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     if args.impl == "reference":
         run_reference(args, rank, world)
@@ -487,7 +497,7 @@ def main():
         }
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline()
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=RESULT_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
