@@ -133,3 +133,57 @@ def test_full_size_rollout_invariants():
     assert bool((m[:, 5:7] == 0).all())                      # hidden opponent types (Geister, player view)
     am = waves['action_mask'][0]
     assert bool(((am == 0) | (am == 1e32)).all()) and bool(((am == 0).sum(1) >= 1).all())
+
+
+_DIGEST_SCRIPT = r"""
+import hashlib, sys, torch
+sys.path.insert(0, %r)
+from handyrl_b200.engine import BatchedEnv
+N, K = 16384, 42
+out = []
+for game in ('Geister', 'TicTacToe'):
+    env = BatchedEnv(game, N)
+    main, scalar = env.alloc_obs(waves=2)
+    waves = dict(main=main, scalar=scalar, action_mask=torch.empty(2, N, env.A, device='cuda'))
+    act = torch.full((K, N), -9, dtype=torch.int32, device='cuda')
+    traj = torch.zeros(N, 64, 8, dtype=torch.int32, device='cuda')
+    ept = torch.zeros(1 << 18, 4, dtype=torch.int32, device='cuda')   # > finished episodes: no ring wrap
+    ctr = torch.zeros(8, dtype=torch.int64, device='cuda')
+    for n in (21, 21):                                  # launches that end inside a 4-ply record group
+        env.rollout(n, seed=11, waves=waves, traj=traj, ep_table=ept, counters=ctr, out_action=act)
+    torch.cuda.synchronize()
+    n_ep = int(ctr[5])
+    assert n_ep <= ept.shape[0]
+    rows = ept[:n_ep].cpu().numpy()
+    rows = rows[rows[:, 0].argsort(kind='stable')]      # append order is not deterministic; content is
+    rows = rows[(rows[:, 2].astype('int64') * N + rows[:, 0]).argsort(kind='stable')]
+    h = hashlib.sha256()
+    for t in (act, traj, env.state, main, waves['action_mask'], ctr[:5]):
+        h.update(t.cpu().numpy().tobytes())
+    if scalar is not None:
+        h.update(scalar.cpu().numpy().tobytes())
+    h.update(rows.tobytes())
+    out.append(h.hexdigest())
+print(' '.join(out))
+"""
+
+
+def test_ticketed_rollout_equals_static_rollout():
+    """N = 16,384 games is above the ticket threshold (2 x SM count groups): the dynamic (group, chunk) schedule
+    must produce exactly what the static one-warp-per-group schedule (B200RL_ROLLOUT_CHUNK=0) produces — moments,
+    records, states, counters and the set of finished episodes."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = {}
+    for name, chunk in (('tickets', None), ('static', '0'), ('tickets8', '8')):
+        env = dict(os.environ)
+        env.pop('B200RL_ROLLOUT_CHUNK', None)
+        if chunk is not None:
+            env['B200RL_ROLLOUT_CHUNK'] = chunk
+        r = subprocess.run([sys.executable, '-c', _DIGEST_SCRIPT % root], env=env, capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        res[name] = r.stdout.strip().splitlines()[-1]
+    assert res['tickets'] == res['static'] == res['tickets8'], res
