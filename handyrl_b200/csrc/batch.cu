@@ -5,6 +5,12 @@
 // state, the action(s) and episode flags.  make_batch re-encodes observation,
 // policy and action_mask from the record instead of copying 2.8 kB of fp32 per
 // (b, t): HBM reads are 32 B per cell, writes are the batch tensors themselves.
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <vector>
+
 #include "common.cuh"
 #include "games.cuh"
 #include "emit.cuh"
@@ -558,8 +564,67 @@ extern "C" int b200rl_select_windows(const int32_t* ep_table, int64_t E, const u
     return b200rl_check_launch("k_select_windows");
 }
 
-#include <thread>
-#include <vector>
+
+// Persistent host worker pool for b200rl_select_windows_host: creating and joining std::threads on every call cost
+// more than the selection itself (8 threads: 0.35 ms per call for 0.19 ms of work).
+namespace {
+class HostPool {
+public:
+    ~HostPool() {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            stop_ = true;
+        }
+        cv_work_.notify_all();
+        for (auto& t : th_) t.join();
+    }
+    // runs f(0..n-1) on n pool threads and returns when all are done; one caller at a time
+    void run(int n, const std::function<void(int)>& f) {
+        std::lock_guard<std::mutex> serial(run_mu_);
+        std::unique_lock<std::mutex> lk(m_);
+        while ((int)th_.size() < n) {
+            const int id = (int)th_.size();
+            th_.emplace_back([this, id] { worker(id); });
+        }
+        job_ = &f;
+        n_active_ = n;
+        pending_ = n;
+        ++generation_;
+        cv_work_.notify_all();
+        cv_done_.wait(lk, [this] { return pending_ == 0; });
+        job_ = nullptr;
+    }
+
+private:
+    void worker(int id) {
+        uint64_t seen = 0;
+        std::unique_lock<std::mutex> lk(m_);
+        for (;;) {
+            cv_work_.wait(lk, [&] { return stop_ || generation_ != seen; });
+            if (stop_) return;
+            seen = generation_;
+            if (id < n_active_) {
+                const std::function<void(int)>* job = job_;
+                lk.unlock();
+                (*job)(id);
+                lk.lock();
+                if (--pending_ == 0) cv_done_.notify_one();
+            }
+        }
+    }
+    std::mutex m_, run_mu_;
+    std::condition_variable cv_work_, cv_done_;
+    std::vector<std::thread> th_;
+    const std::function<void(int)>* job_ = nullptr;
+    int n_active_ = 0, pending_ = 0;
+    uint64_t generation_ = 0;
+    bool stop_ = false;
+};
+HostPool& host_pool() {
+    static HostPool pool;
+    return pool;
+}
+}  // namespace
 
 extern "C" int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t E, uint64_t cursor,
                                           int64_t maximum_episodes, int64_t forward_steps, uint64_t seed,
@@ -579,13 +644,11 @@ extern "C" int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t 
         work(0, B);
         return B200RL_OK;
     }
-    std::vector<std::thread> th;
     const int64_t per = (B + n_threads - 1) / n_threads;
-    for (int t = 0; t < n_threads; ++t) {
+    host_pool().run(n_threads, [&](int t) {
         const int64_t lo = t * per, hi = lo + per < B ? lo + per : B;
-        if (lo < hi) th.emplace_back(work, lo, hi);
-    }
-    for (auto& x : th) x.join();
+        if (lo < hi) work(lo, hi);
+    });
     return B200RL_OK;
 }
 
