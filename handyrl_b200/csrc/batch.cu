@@ -18,13 +18,7 @@
 
 namespace {
 
-#ifndef B200RL_MB_BLK
-#define B200RL_MB_BLK 128
-#endif
-#ifndef B200RL_MB_MINB
-#define B200RL_MB_MINB 1
-#endif
-constexpr int BLK = B200RL_MB_BLK;
+constexpr int BLK = 128;
 constexpr int WARPS = BLK / 32;
 
 // ---------------------------------------------------------------------------
@@ -217,7 +211,7 @@ __device__ __forceinline__ void pack_rows(uint32_t* flat, int lane, int Po, int 
 }
 
 template <class G>
-__global__ void __launch_bounds__(BLK, B200RL_MB_MINB) k_make_batch(const BatchParams p) {
+__global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
     __shared__ BatchCta<G> cta;
     nibble_table_init(cta.tbl_obs, 0.f, 1.f, threadIdx.x);
     nibble_table_init(cta.tbl_amask, 1e32f, 0.f, threadIdx.x);
@@ -243,11 +237,7 @@ __global__ void __launch_bounds__(BLK, B200RL_MB_MINB) k_make_batch(const BatchP
 #pragma unroll
         for (int k = 0; k < G::LW; ++k) lg[q][k] = il[q][k] = 0;
     }
-#ifdef B200RL_MB_PROBE   // timing experiment only: no gathers, no per-cell work, just the emit pattern
-    if (false) {
-#else
     if (valid) {
-#endif
         const int64_t b = c / p.T;
         const int t = (int)(c - b * p.T);
         const int32_t* w = p.win + b * 8;
@@ -261,11 +251,7 @@ __global__ void __launch_bounds__(BLK, B200RL_MB_MINB) k_make_batch(const BatchP
             const uint64_t it = ((uint64_t)(uint32_t)w[1] | ((uint64_t)(uint32_t)w[2] << 32)) + (uint64_t)t;
             const int64_t slot = w[0];
             uint32_t rec[8];
-#ifdef B200RL_MB_PROBE2   // timing experiment only: coalesced record reads
-            ld_record(p.traj, p.D, p.N, 0, c % p.N, rec);
-#else
             ld_record(p.traj, p.D, p.N, it, slot, rec);
-#endif
             typename G::State s = G::unpack_record(rec);
             const int tp = G::turn(s);  // m['turn'][0]
             const bool parallel = G::SIMULTANEOUS;
