@@ -296,12 +296,18 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
         }
         // ---- small per-cell tensors ----
         for (int q = 0; q < Po; ++q) p.action[c * Po + q] = act[q];
-        for (int q = 0; q < Pv; ++q) {
-            p.value[c * Pv + q] = val[q];
-            p.reward[c * Pv + q] = rew[q];
-            p.ret[c * Pv + q] = rtn[q];
-            p.tmask[c * Pv + q] = tm[q];
-            p.omask[c * Pv + q] = om[q];
+        if (Pv == 2) {   // both players of a cell in one 8-byte store: a warp writes 256 contiguous bytes per tensor
+            *reinterpret_cast<float2*>(p.value + c * 2) = make_float2(val[0], val[1]);
+            *reinterpret_cast<float2*>(p.reward + c * 2) = make_float2(rew[0], rew[1]);
+            *reinterpret_cast<float2*>(p.ret + c * 2) = make_float2(rtn[0], rtn[1]);
+            *reinterpret_cast<float2*>(p.tmask + c * 2) = make_float2(tm[0], tm[1]);
+            *reinterpret_cast<float2*>(p.omask + c * 2) = make_float2(om[0], om[1]);
+        } else {
+            p.value[c] = val[0];
+            p.reward[c] = rew[0];
+            p.ret[c] = rtn[0];
+            p.tmask[c] = tm[0];
+            p.omask[c] = om[0];
         }
         p.emask[c] = live ? 1.f : 0.f;
         p.progress[c] = live ? __fdiv_rn((float)(stt + t), (float)total) : 1.f;
@@ -526,6 +532,9 @@ extern "C" int b200rl_make_batch(int game, const void* traj, int64_t D, int64_t 
     B200RL_REQUIRE(ret_table && ret_len >= 1, "make_batch: null return table");
     B200RL_REQUIRE(((uintptr_t)obs_main % 16) == 0 && ((uintptr_t)policy % 16) == 0 && ((uintptr_t)amask % 16) == 0 &&
                        ((uintptr_t)obs_scalar % 16) == 0, "make_batch: outputs must be 16-byte aligned");
+    B200RL_REQUIRE(((uintptr_t)value % 8) == 0 && ((uintptr_t)reward % 8) == 0 && ((uintptr_t)ret % 8) == 0 &&
+                       ((uintptr_t)tmask % 8) == 0 && ((uintptr_t)omask % 8) == 0 && ((uintptr_t)windows % 16) == 0,
+                   "make_batch: value/reward/return/masks must be 8-byte aligned, windows 16-byte aligned");
     if (B == 0) return B200RL_OK;
     BatchParams p;
     p.traj = (const uint4*)traj; p.D = D; p.N = N; p.values = values; p.logits = logits; p.win = windows;
