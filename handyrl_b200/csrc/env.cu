@@ -342,15 +342,17 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                               p.out_scalar ? p.out_scalar + wv * p.N * G::SBITS : nullptr,
                               p.out_amask ? p.out_amask + wv * p.N * G::A : nullptr, nullptr);
             }
+            bool term = false;
+            uint32_t wincode = 0;
             if (valid) {
                 if (p.out_action) p.out_action[wv * p.N + i] = action;
                 uint32_t rec[8];
                 if (p.traj) G::pack_record(s, rec);
                 G::step(s, action, selp);
-                const bool term = G::terminal(s);
+                term = G::terminal(s);
                 float o0 = 0.f, o1 = 0.f;
                 if (term) G::outcome(s, o0, o1);
-                const uint32_t wincode = term ? (o0 > 0 ? 1u : (o1 > 0 ? 2u : 3u)) : 0u;
+                wincode = term ? (o0 > 0 ? 1u : (o1 > 0 ? 2u : 3u)) : 0u;
                 if (p.traj) {
                     rec[5] = ((uint32_t)action & 0xFFFF) | ((uint32_t)selp << 16) | ((first ? 1u : 0u) << 24) |
                              ((term ? 1u : 0u) << 25) | (wincode << 26);
@@ -365,13 +367,25 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                     n_w0 += wincode == 1;
                     n_w1 += wincode == 2;
                     n_dr += wincode == 3;
-                    if (p.ep_table) {
-                        unsigned long long idx = atomicAdd(&p.counters[5], 1ull);
-                        int32_t* e = p.ep_table + (int64_t)(idx % (unsigned long long)p.E) * 4;
-                        e[0] = (int32_t)i;
-                        e[1] = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
-                        e[2] = (int32_t)(uint32_t)it;
-                        e[3] = (int32_t)(uint32_t)(it >> 32);
+                }
+            }
+            if (p.ep_table) {
+                // episode-table append, one atomic per warp and ply: TicTacToe finishes ~4 of a warp's 32 games every
+                // ply, and 3 G same-address atomics per second was what bounded its rollout
+                const unsigned int fin = __ballot_sync(0xffffffffu, term);
+                if (fin) {
+                    const int leader = __ffs(fin) - 1;
+                    unsigned long long base = 0;
+                    if (lane == leader) base = atomicAdd(&p.counters[5], (unsigned long long)__popc(fin));
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    if (term) {
+                        const unsigned long long idx = base + (unsigned long long)__popc(fin & ((1u << lane) - 1u));
+                        int4 row;
+                        row.x = (int32_t)i;
+                        row.y = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
+                        row.z = (int32_t)(uint32_t)it;
+                        row.w = (int32_t)(uint32_t)(it >> 32);
+                        *reinterpret_cast<int4*>(p.ep_table + (int64_t)(idx % (unsigned long long)p.E) * 4) = row;
                     }
                 }
             }
@@ -425,6 +439,19 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
 }
 
 inline int grid_for(int64_t N) { return (int)((N + BLK - 1) / BLK); }
+
+// persistent grid: as many CTAs as are resident at once (8 per SM for Geister at 128 registers, more for TicTacToe)
+template <class G>
+void launch_rollout(const RolloutParams& p, int64_t want, int sms, cudaStream_t stream) {
+    static int per_sm = 0;
+    if (per_sm == 0) {
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_rollout<G>, BLK, 0) != cudaSuccess || n < 1) n = 8;
+        per_sm = n;
+    }
+    const int grid = (int)min(want, (int64_t)sms * per_sm);
+    k_rollout<G><<<grid, BLK, 0, stream>>>(p);
+}
 
 }  // namespace
 
@@ -561,6 +588,7 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     B200RL_REQUIRE(!(out_main || out_scalar || out_amask || out_action) || waves >= 1, "env_rollout: waves must be >= 1");
     B200RL_REQUIRE(!traj || D >= 1, "env_rollout: trajectory ring depth D must be >= 1");
     B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_rollout: episode table needs E >= 1 and counters");
+    B200RL_REQUIRE(((uintptr_t)ep_table % 16) == 0, "env_rollout: episode table must be 16-byte aligned");
     B200RL_REQUIRE(N % 2 == 0 || waves <= 1 || !(out_main || out_scalar || out_amask),
                    "env_rollout: N must be even when several waves are written (16-byte aligned wave bases)");
     RolloutParams p;
@@ -598,7 +626,6 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     p.sched = sched;
     p.chunk = chunk;
     const int64_t want = (ngroups + WARPS - 1) / WARPS;
-    const int grid = (int)min(want, (int64_t)sms * 8);   // persistent: at most __launch_bounds__(BLK, 8) CTAs per SM
-    DISPATCH_GAME(game, (k_rollout<G><<<grid, BLK, 0, (cudaStream_t)stream>>>(p)));
+    DISPATCH_GAME(game, launch_rollout<G>(p, want, sms, (cudaStream_t)stream));
     return b200rl_check_launch("k_rollout");
 }

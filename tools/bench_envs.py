@@ -10,7 +10,7 @@ import torch  # noqa: E402
 
 from handyrl_b200.generation import BatchGenerator  # noqa: E402
 
-N = 65536
+N = int(os.environ.get('BENCH_ENVS_N', 65536))
 BYTES = {"TicTacToe": 108 + 36 + 4 + 32, "ParallelTicTacToe": 108 + 36 + 4 + 32, "Geister": 1940 + 32,
          "CIGeister": 1940 + 32}
 
