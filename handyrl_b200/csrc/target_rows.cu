@@ -296,6 +296,219 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Warp-specialised variant for FEW tiles (small B, long rows): the recursion is then bounded by the sequential
+// depth of one warp, not by memory (profiles/r1_target_rows_smallB.md: a lone warp issues the ~30 instructions of
+// a V-Trace timestep for two players at 0.3 IPC = 48 ns per timestep).  Here a CTA is two warps:
+//   warp 0 (I/O)      cp.async ring fetch of the chunks and the 128-bit streaming flush of finished chunks;
+//   warp 1 (compute)  lane = (row, player): ONE sequence per lane, so a timestep is half the instructions, and
+//                     none of the copy instructions sit between two steps of the dependent fp32 chain.
+// The warps hand chunks over through two mbarriers per ring slot (full: data landed, done: results written).
+// Same tiles, same Rec<> arithmetic, same bits as k_target_rows.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+            : "=r"(ok)
+            : "r"(smem_u32(b)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+// wait until at most n (0..6, warp-uniform) commit groups are pending
+__device__ __forceinline__ void cp_async_wait_upto(int n) {
+    switch (n) {
+        case 0: cp_async_wait<0>(); break;
+        case 1: cp_async_wait<1>(); break;
+        case 2: cp_async_wait<2>(); break;
+        case 3: cp_async_wait<3>(); break;
+        case 4: cp_async_wait<4>(); break;
+        case 5: cp_async_wait<5>(); break;
+        default: cp_async_wait<6>(); break;
+    }
+}
+
+constexpr int WS_MAX_STAGES = 8;
+constexpr size_t WS_SMEM_CAP = 227 * 1024;             // opt-in dynamic shared memory per CTA on sm_100
+constexpr int WS_BAR_FLOATS = 2 * WS_MAX_STAGES * 2;   // 2 x 8 mbarriers of 8 bytes, in floats
+
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC>
+__global__ void __launch_bounds__(64) k_target_rows_ws(const ScanParams k, int c_alias, int ns) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int TR = 32 / P;                       // rows per tile: one lane per (row, player)
+    constexpr int RSV = RTC * P + 4;
+    constexpr int WR = RHO_PP ? P : 1;
+    constexpr int RSR = RTC * WR + 4;
+    const int STAGE = TR * (2 * RSV + (NEED_RHO ? (c_alias ? RSR : 2 * RSR) : 0));
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+    uint64_t* done = full + WS_MAX_STAGES;
+    float* ring = smem + WS_BAR_FLOATS;
+    const int lane = threadIdx.x & 31;
+    const int b0 = blockIdx.x * TR;
+    const int rows = min(TR, k.B - b0);
+    const int n = (k.T + RTC - 1) / RTC;             // chunks, processed in order i = 0..n-1 <-> ch = n-1-i
+    const int64_t row_out = (int64_t)k.T * P;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < ns; ++s) {
+            mbar_init(full + s, 32);
+            mbar_init(done + s, 32);
+        }
+    }
+    __syncthreads();
+
+    if (threadIdx.x < 32) {
+        // ---------------- I/O warp ----------------
+        LaneIO<P, TR, RTC> io_v, io_r, io_o;
+        LaneIO<WR, TR, RTC> io_rho, io_c;
+        io_v.init(k.v.sb, b0, lane);
+        io_o.init(row_out, b0, lane);
+        if (HAS_REW) io_r.init(k.rew.sb, b0, lane);
+        if (NEED_RHO) {
+            io_rho.init(k.rho.sb, b0, lane);
+            io_c.init(k.c.sb, b0, lane);
+        }
+        auto fetch = [&](int i) {
+            if (i < n) {
+                const int ch = n - 1 - i;
+                float* st = ring + (i % ns) * STAGE;
+                const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
+                if (tl == RTC) {
+                    fetch_full<P, RSV, TR, RTC>(st, k.v.p, io_v, rows, t0, lane);
+                    if (HAS_REW) fetch_full<P, RSV, TR, RTC>(st + TR * RSV, k.rew.p, io_r, rows, t0, lane);
+                    if (NEED_RHO) {
+                        fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV, k.rho.p, io_rho, rows, t0, lane);
+                        if (!c_alias) fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV + TR * RSR, k.c.p, io_c, rows, t0, lane);
+                    }
+                } else {
+                    fetch_tile<P, RSV>(st, k.v.p, k.v.sb, b0, rows, t0, tl, lane);
+                    if (HAS_REW) fetch_tile<P, RSV>(st + TR * RSV, k.rew.p, k.rew.sb, b0, rows, t0, tl, lane);
+                    if (NEED_RHO) {
+                        fetch_tile<WR, RSR>(st + 2 * TR * RSV, k.rho.p, k.rho.sb, b0, rows, t0, tl, lane);
+                        if (!c_alias) fetch_tile<WR, RSR>(st + 2 * TR * RSV + TR * RSR, k.c.p, k.c.sb, b0, rows, t0, tl, lane);
+                    }
+                }
+            }
+            cp_async_commit();
+        };
+        auto flush = [&](int i) {
+            mbar_wait(done + (i % ns), (uint32_t)((i / ns) & 1));
+            const int ch = n - 1 - i;
+            const float* st = ring + (i % ns) * STAGE;
+            const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
+            if (tl == RTC) {
+                flush_full<P, RSV, TR, RTC>(st + TR * RSV, k.out_t, io_o, rows, t0, lane);
+                flush_full<P, RSV, TR, RTC>(st, k.out_a, io_o, rows, t0, lane);
+            } else {
+                flush_tile<P, RSV>(st + TR * RSV, k.out_t, row_out, b0, rows, t0, tl, lane);
+                flush_tile<P, RSV>(st, k.out_a, row_out, b0, rows, t0, tl, lane);
+            }
+            __syncwarp();   // every lane has read the slot before any lane's cp.async refills it
+        };
+        for (int j = 0; j < ns - 1; ++j) fetch(j);
+        for (int i = 0; i < n; ++i) {
+            cp_async_wait_upto(ns - 2);          // groups i+1 .. i+ns-2 may still be in flight: chunk i has landed
+            mbar_arrive(full + (i % ns));        // 32 arrivals (release): each lane vouches for its own copies
+            if (i >= 1) flush(i - 1);
+            fetch(i + ns - 1);                   // refills the slot of chunk i-1
+        }
+        flush(n - 1);
+    } else {
+        // ---------------- compute warp: lane = (row, player) ----------------
+        const int r = lane / P, p = lane % P;
+        const bool active = r < rows;
+        const float R = active ? k.boot[(int64_t)(b0 + r) * k.boot_sb + (int64_t)p * k.boot_sp] : 0.f;
+        Rec<MT> rec_t;
+        Rec<MA> rec_a;
+        struct Grp { float v[4], r[4], rho[4], c[4]; };
+        for (int i = 0; i < n; ++i) {
+            const int ch = n - 1 - i;
+            float* st = ring + (i % ns) * STAGE;
+            const int tl = min(RTC, k.T - ch * RTC);
+            mbar_wait(full + (i % ns), (uint32_t)((i / ns) & 1));
+            if (active) {
+                float* pv = st + r * RSV + p;
+                float* pr = st + TR * RSV + r * RSV + p;
+                const float* prho = st + 2 * TR * RSV + r * RSR + (RHO_PP ? p : 0);
+                const float* pc = prho + TR * RSR;
+                auto load_group = [&](Grp& g, int q) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        g.v[j] = pv[(q * 4 + j) * P];
+                        if (HAS_REW) g.r[j] = pr[(q * 4 + j) * P];
+                    }
+                    if (NEED_RHO) {
+                        if (WR == 1) {   // rho / c broadcast over players: 4 steps are one 16-byte unit
+                            const float4 a = *reinterpret_cast<const float4*>(prho + q * 4);
+                            g.rho[0] = a.x; g.rho[1] = a.y; g.rho[2] = a.z; g.rho[3] = a.w;
+                            if (!c_alias) {
+                                const float4 b = *reinterpret_cast<const float4*>(pc + q * 4);
+                                g.c[0] = b.x; g.c[1] = b.y; g.c[2] = b.z; g.c[3] = b.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                g.rho[j] = prho[(q * 4 + j) * WR];
+                                if (!c_alias) g.c[j] = pc[(q * 4 + j) * WR];
+                            }
+                        }
+                    }
+                };
+                auto compute_group = [&](const Grp& g, int q, auto first_tag) {
+                    constexpr bool FIRST = decltype(first_tag)::value;
+#pragma unroll
+                    for (int j = 3; j >= 0; --j) {
+                        const float r_ = HAS_REW ? g.r[j] : 0.f;
+                        const float rh = NEED_RHO ? g.rho[j] : 0.f;
+                        const float c_ = NEED_RHO ? (c_alias ? g.rho[j] : g.c[j]) : 0.f;
+                        float t1, a1, t2, a2;
+                        if (FIRST && j == 3) {
+                            rec_t.first(g.v[j], r_, rh, c_, R, k, t1, a1);
+                            if (MT != MA) {
+                                rec_a.first(g.v[j], r_, rh, c_, R, k, t2, a2);
+                                a1 = a2;
+                            }
+                        } else {
+                            rec_t.next(g.v[j], r_, rh, c_, k, t1, a1);
+                            if (MT != MA) {
+                                rec_a.next(g.v[j], r_, rh, c_, k, t2, a2);
+                                a1 = a2;
+                            }
+                        }
+                        pv[(q * 4 + j) * P] = a1;
+                        pr[(q * 4 + j) * P] = t1;
+                    }
+                };
+                Grp ga, gb;
+                int q = (tl >> 2) - 1;
+                load_group(ga, q);
+                if (i == 0) {
+                    if (q >= 1) load_group(gb, q - 1);
+                    compute_group(ga, q, std::true_type{});
+                    --q;
+                    if (q >= 0) ga = gb;
+                }
+                for (; q >= 1; q -= 2) {
+                    load_group(gb, q - 1);
+                    compute_group(ga, q, std::false_type{});
+                    if (q >= 2) load_group(ga, q - 2);
+                    compute_group(gb, q - 1, std::false_type{});
+                }
+                if (q == 0) compute_group(ga, 0, std::false_type{});
+            }
+            mbar_arrive(done + (i % ns));
+        }
+    }
+}
+
 }  // namespace
 
 namespace {
@@ -340,10 +553,61 @@ int launch_shape(const ScanParams& k, cudaStream_t st) {
     return b200rl_check_launch("k_target_rows");
 }
 
+// Warp-specialised launch (k_target_rows_ws): one CTA of two warps per tile of 32/P rows, ring as deep as the
+// shared memory allows for the number of CTAs an SM has to hold.
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC>
+int launch_ws(const ScanParams& k, cudaStream_t st) {
+    constexpr int TR = 32 / P;
+    constexpr int RSV = RTC * P + 4;
+    constexpr int RSR = RTC * (RHO_PP ? P : 1) + 4;
+    const bool alias = NEED_RHO && k.c.p == k.rho.p && k.c.sb == k.rho.sb && k.c.st == k.rho.st && k.c.sp == k.rho.sp;
+    const size_t stage = sizeof(float) * TR * (2 * RSV + (NEED_RHO ? (alias ? RSR : 2 * RSR) : 0));
+    auto kern = k_target_rows_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, RTC>;
+    constexpr size_t BAR = WS_BAR_FLOATS * sizeof(float);
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        constexpr size_t SMEM_ALL = BAR + (size_t)WS_MAX_STAGES * sizeof(float) * TR * (2 * RSV + 2 * RSR);
+        constexpr size_t SMEM_MAX = SMEM_ALL < WS_SMEM_CAP ? SMEM_ALL : WS_SMEM_CAP;
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+    }
+    const int ntiles = (k.B + TR - 1) / TR;
+    const int want = (ntiles + sms - 1) / sms;   // CTAs an SM holds when the whole grid is resident
+    const char* ns_e = getenv("B200RL_TARGET_WS_STAGES");
+    const int ns_env = ns_e ? atoi(ns_e) : 0;
+    int ns = 3;
+    while (ns < WS_MAX_STAGES && (size_t)want * (BAR + (ns + 1) * stage + 1024) <= (size_t)220 * 1024) ++ns;
+    if (ns_env >= 2 && ns_env <= WS_MAX_STAGES) ns = ns_env;
+    while (ns > 2 && BAR + ns * stage > WS_SMEM_CAP) --ns;
+    kern<<<ntiles, 64, BAR + ns * stage, st>>>(k, alias ? 1 : 0, ns);
+    return b200rl_check_launch("k_target_rows_ws");
+}
+
+// B200RL_TARGET_WS=0 / 1 forces the one-warp / warp-specialised kernel for A/B measurements; by default the
+// warp-specialised one takes the launches with few tiles (see ws_tiles_max), where the sequential depth of a warp
+// and not HBM is the bound.
+// (read at every call, so that a test can switch kernels inside one process)
+inline int ws_mode() {
+    const char* e = getenv("B200RL_TARGET_WS");
+    return e ? atoi(e) : -1;
+}
+inline int ws_tiles_max() {
+    const char* e = getenv("B200RL_TARGET_WS_TILES");
+    return e ? atoi(e) : 1184;
+}
+
 // long rows: 16-row tiles, 256 B per row per fetch (32 steps at P = 2, 64 at P = 1); rows of <= 64 steps: 32 x 16
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
 int launch_rows(const ScanParams& k, cudaStream_t st) {
-    if (k.T > B200RL_SHORT_T) return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 16, 64 / P>(k, st);
+    if (k.T > B200RL_SHORT_T) {
+        const int wm = ws_mode();
+        const int ws_tiles = (k.B + 32 / P - 1) / (32 / P);
+        if (wm == 1 || (wm < 0 && ws_tiles <= ws_tiles_max()))
+            return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P>(k, st);
+        return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 16, 64 / P>(k, st);
+    }
     return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 32, 16>(k, st);
 }
 
