@@ -301,10 +301,14 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
 // Warp-specialised variant for FEW tiles (small B, long rows): the recursion is then bounded by the sequential
 // depth of one warp, not by memory (profiles/r1_target_rows_smallB.md: a lone warp issues the ~30 instructions of
 // a V-Trace timestep for two players at 0.3 IPC = 48 ns per timestep).  Here a CTA is two warps:
-//   warp 0 (I/O)      cp.async ring fetch of the chunks and the 128-bit streaming flush of finished chunks;
+//   warp 0 (I/O)      lane r owns batch row r of the tile and moves its slices with the bulk-copy engine (TMA,
+//                     non-tensor form): one cp.async.bulk per row and array into the ring slot, completion counted
+//                     in bytes on the slot's `full` mbarrier; finished slots leave as bulk stores shared -> global.
+//                     That is ~10 instructions per chunk and lane (the LDGSTS/LDS+STG version of this warp was
+//                     460 per chunk and the bottleneck: profiles/r1_target_rows_ws.md);
 //   warp 1 (compute)  lane = (row, player): ONE sequence per lane, so a timestep is half the instructions, and
-//                     none of the copy instructions sit between two steps of the dependent fp32 chain.
-// The warps hand chunks over through two mbarriers per ring slot (full: data landed, done: results written).
+//                     no copy instruction sits between two steps of the dependent fp32 chain.
+// Hand-over through two mbarriers per ring slot (full: bytes landed, done: results written + proxy fence).
 // Same tiles, same Rec<> arithmetic, same bits as k_target_rows.
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
@@ -312,6 +316,9 @@ __device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* b) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
     uint32_t ok;
@@ -323,18 +330,30 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
             : "memory");
     } while (!ok);
 }
-// wait until at most n (0..6, warp-uniform) commit groups are pending
-__device__ __forceinline__ void cp_async_wait_upto(int n) {
-    switch (n) {
-        case 0: cp_async_wait<0>(); break;
-        case 1: cp_async_wait<1>(); break;
-        case 2: cp_async_wait<2>(); break;
-        case 3: cp_async_wait<3>(); break;
-        case 4: cp_async_wait<4>(); break;
-        case 5: cp_async_wait<5>(); break;
-        default: cp_async_wait<6>(); break;
-    }
+// bulk copy global -> shared, completion (bytes) signalled on an mbarrier; 16-byte aligned, size % 16 == 0
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
 }
+// bulk copy shared -> global, tracked by the issuing thread's bulk async-group
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {   // all but the N latest groups have finished READING shared
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait() {
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+// generic-proxy writes to shared (STS) -> visible to the async proxy (bulk store) that reads them next
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 constexpr int WS_MAX_STAGES = 8;
 constexpr size_t WS_SMEM_CAP = 227 * 1024;             // opt-in dynamic shared memory per CTA on sm_100
@@ -366,61 +385,63 @@ __global__ void __launch_bounds__(64) k_target_rows_ws(const ScanParams k, int c
     __syncthreads();
 
     if (threadIdx.x < 32) {
-        // ---------------- I/O warp ----------------
-        LaneIO<P, TR, RTC> io_v, io_r, io_o;
-        LaneIO<WR, TR, RTC> io_rho, io_c;
-        io_v.init(k.v.sb, b0, lane);
-        io_o.init(row_out, b0, lane);
-        if (HAS_REW) io_r.init(k.rew.sb, b0, lane);
-        if (NEED_RHO) {
-            io_rho.init(k.rho.sb, b0, lane);
-            io_c.init(k.c.sb, b0, lane);
-        }
+        // ---------------- I/O warp: lane = batch row ----------------
+        const bool own = lane < rows;
+        const int64_t rb = b0 + (own ? lane : 0);
+        const float* gv = k.v.p + rb * k.v.sb;
+        const float* gr = HAS_REW ? k.rew.p + rb * k.rew.sb : nullptr;
+        const float* grho = NEED_RHO ? k.rho.p + rb * k.rho.sb : nullptr;
+        const float* gc = NEED_RHO ? k.c.p + rb * k.c.sb : nullptr;
+        float* ot = k.out_t + rb * row_out;
+        float* oa = k.out_a + rb * row_out;
+        float* sv = ring + lane * RSV;                     // this row in slot 0: values / advantages
+        float* sr = ring + TR * RSV + lane * RSV;          //                     rewards / targets
+        float* srho = ring + 2 * TR * RSV + lane * RSR;
+        float* sc = srho + TR * RSR;
+        int fslot = 0;                                     // slot of the next fetch
         auto fetch = [&](int i) {
-            if (i < n) {
-                const int ch = n - 1 - i;
-                float* st = ring + (i % ns) * STAGE;
-                const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
-                if (tl == RTC) {
-                    fetch_full<P, RSV, TR, RTC>(st, k.v.p, io_v, rows, t0, lane);
-                    if (HAS_REW) fetch_full<P, RSV, TR, RTC>(st + TR * RSV, k.rew.p, io_r, rows, t0, lane);
-                    if (NEED_RHO) {
-                        fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV, k.rho.p, io_rho, rows, t0, lane);
-                        if (!c_alias) fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV + TR * RSR, k.c.p, io_c, rows, t0, lane);
-                    }
-                } else {
-                    fetch_tile<P, RSV>(st, k.v.p, k.v.sb, b0, rows, t0, tl, lane);
-                    if (HAS_REW) fetch_tile<P, RSV>(st + TR * RSV, k.rew.p, k.rew.sb, b0, rows, t0, tl, lane);
-                    if (NEED_RHO) {
-                        fetch_tile<WR, RSR>(st + 2 * TR * RSV, k.rho.p, k.rho.sb, b0, rows, t0, tl, lane);
-                        if (!c_alias) fetch_tile<WR, RSR>(st + 2 * TR * RSV + TR * RSR, k.c.p, k.c.sb, b0, rows, t0, tl, lane);
-                    }
+            const int t0 = (n - 1 - i) * RTC, tl = min(RTC, k.T - t0);
+            uint64_t* bar = full + fslot;
+            if (own) {
+                const uint32_t bv = tl * P * 4, br = tl * WR * 4;
+                mbar_arrive_expect_tx(bar, bv * (HAS_REW ? 2 : 1) + (NEED_RHO ? br * (c_alias ? 1 : 2) : 0));
+                const int so = fslot * STAGE;
+                bulk_g2s(sv + so, gv + t0 * P, bv, bar);
+                if (HAS_REW) bulk_g2s(sr + so, gr + t0 * P, bv, bar);
+                if (NEED_RHO) {
+                    bulk_g2s(srho + so, grho + t0 * WR, br, bar);
+                    if (!c_alias) bulk_g2s(sc + so, gc + t0 * WR, br, bar);
                 }
-            }
-            cp_async_commit();
-        };
-        auto flush = [&](int i) {
-            mbar_wait(done + (i % ns), (uint32_t)((i / ns) & 1));
-            const int ch = n - 1 - i;
-            const float* st = ring + (i % ns) * STAGE;
-            const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
-            if (tl == RTC) {
-                flush_full<P, RSV, TR, RTC>(st + TR * RSV, k.out_t, io_o, rows, t0, lane);
-                flush_full<P, RSV, TR, RTC>(st, k.out_a, io_o, rows, t0, lane);
             } else {
-                flush_tile<P, RSV>(st + TR * RSV, k.out_t, row_out, b0, rows, t0, tl, lane);
-                flush_tile<P, RSV>(st, k.out_a, row_out, b0, rows, t0, tl, lane);
+                mbar_arrive(bar);
             }
-            __syncwarp();   // every lane has read the slot before any lane's cp.async refills it
+            if (++fslot == ns) fslot = 0;
         };
-        for (int j = 0; j < ns - 1; ++j) fetch(j);
+        const int pre = min(ns, n);                        // every slot starts loaded
+        for (int j = 0; j < pre; ++j) fetch(j);
+        int slot = 0;
+        uint32_t par = 0;
         for (int i = 0; i < n; ++i) {
-            cp_async_wait_upto(ns - 2);          // groups i+1 .. i+ns-2 may still be in flight: chunk i has landed
-            mbar_arrive(full + (i % ns));        // 32 arrivals (release): each lane vouches for its own copies
-            if (i >= 1) flush(i - 1);
-            fetch(i + ns - 1);                   // refills the slot of chunk i-1
+            mbar_wait(done + slot, par);
+            if (own) {
+                const int t0 = (n - 1 - i) * RTC, tl = min(RTC, k.T - t0);
+                const uint32_t bv = tl * P * 4;
+                const int so = slot * STAGE;
+                bulk_s2g(ot + t0 * P, sr + so, bv);
+                bulk_s2g(oa + t0 * P, sv + so, bv);
+            }
+            bulk_commit();
+            // the slot of chunk i-1 can be refilled once ITS stores have read it: leave the latest group pending
+            if (i >= 1 && i - 1 + ns < n) {
+                bulk_wait_read<1>();
+                fetch(i - 1 + ns);
+            }
+            if (++slot == ns) {
+                slot = 0;
+                par ^= 1;
+            }
         }
-        flush(n - 1);
+        bulk_wait<0>();
     } else {
         // ---------------- compute warp: lane = (row, player) ----------------
         const int r = lane / P, p = lane % P;
@@ -429,11 +450,13 @@ __global__ void __launch_bounds__(64) k_target_rows_ws(const ScanParams k, int c
         Rec<MT> rec_t;
         Rec<MA> rec_a;
         struct Grp { float v[4], r[4], rho[4], c[4]; };
+        int slot = 0;
+        uint32_t par = 0;
         for (int i = 0; i < n; ++i) {
             const int ch = n - 1 - i;
-            float* st = ring + (i % ns) * STAGE;
+            float* st = ring + slot * STAGE;
             const int tl = min(RTC, k.T - ch * RTC);
-            mbar_wait(full + (i % ns), (uint32_t)((i / ns) & 1));
+            mbar_wait(full + slot, par);
             if (active) {
                 float* pv = st + r * RSV + p;
                 float* pr = st + TR * RSV + r * RSV + p;
@@ -504,7 +527,12 @@ __global__ void __launch_bounds__(64) k_target_rows_ws(const ScanParams k, int c
                 }
                 if (q == 0) compute_group(ga, 0, std::false_type{});
             }
-            mbar_arrive(done + (i % ns));
+            fence_proxy_async();
+            mbar_arrive(done + slot);
+            if (++slot == ns) {
+                slot = 0;
+                par ^= 1;
+            }
         }
     }
 }
