@@ -88,6 +88,12 @@ struct LaneIO {
     }
 };
 
+__device__ __forceinline__ void cp_async16_s(uint32_t smem_addr, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
+}
+
+// Running pointers (one 64-bit add per row) and a predicate-free path for full tiles: the copy instructions share
+// the warp's issue slots with the recursion, so their address arithmetic is kept to two instructions per 16 bytes.
 template <int W, int RS, int TR, int RTC>
 __device__ __forceinline__ void fetch_full(float* tile, const float* __restrict__ g, const LaneIO<W, TR, RTC>& io,
                                            int rows, int t0, int lane) {
@@ -95,10 +101,20 @@ __device__ __forceinline__ void fetch_full(float* tile, const float* __restrict_
     constexpr int U = IO::U, RPI = IO::RPI, NI = IO::NI;
     const int r0 = lane / U;
     const float* p = g + io.off + t0 * W;
-    float* s = tile + r0 * RS + (lane % U) * 4;
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(tile + r0 * RS + (lane % U) * 4);
+    if (rows == TR) {
 #pragma unroll
-    for (int i = 0; i < NI; ++i)
-        if (r0 + i * RPI < rows) cp_async16(s + i * RPI * RS, p + i * io.step);
+        for (int i = 0; i < NI; ++i) {
+            cp_async16_s(s + i * RPI * RS * 4, p);
+            p += io.step;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            if (r0 + i * RPI < rows) cp_async16_s(s + i * RPI * RS * 4, p);
+            p += io.step;
+        }
+    }
 }
 
 template <int W, int RS, int TR, int RTC>
@@ -109,10 +125,20 @@ __device__ __forceinline__ void flush_full(const float* tile, float* __restrict_
     const int r0 = lane / U;
     float* p = out + io.off + t0 * W;
     const float* s = tile + r0 * RS + (lane % U) * 4;
+    if (rows == TR) {
 #pragma unroll
-    for (int i = 0; i < NI; ++i)
-        if (r0 + i * RPI < rows)
-            st_stream_f4(reinterpret_cast<float4*>(p + i * io.step), *reinterpret_cast<const float4*>(s + i * RPI * RS));
+        for (int i = 0; i < NI; ++i) {
+            st_stream_f4(reinterpret_cast<float4*>(p), *reinterpret_cast<const float4*>(s + i * RPI * RS));
+            p += io.step;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            if (r0 + i * RPI < rows)
+                st_stream_f4(reinterpret_cast<float4*>(p), *reinterpret_cast<const float4*>(s + i * RPI * RS));
+            p += io.step;
+        }
+    }
 }
 
 // Four timesteps (descending) of the P sequences of one row.  FIRST: the group contains t = T-1 at j = 3.
@@ -300,15 +326,17 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
 // ---------------------------------------------------------------------------------------------------------------
 // Warp-specialised variant for FEW tiles (small B, long rows): the recursion is then bounded by the sequential
 // depth of one warp, not by memory (profiles/r1_target_rows_smallB.md: a lone warp issues the ~30 instructions of
-// a V-Trace timestep for two players at 0.3 IPC = 48 ns per timestep).  Here a CTA is two warps:
-//   warp 0 (I/O)      lane r owns batch row r of the tile and moves its slices with the bulk-copy engine (TMA,
-//                     non-tensor form): one cp.async.bulk per row and array into the ring slot, completion counted
-//                     in bytes on the slot's `full` mbarrier; finished slots leave as bulk stores shared -> global.
-//                     That is ~10 instructions per chunk and lane (the LDGSTS/LDS+STG version of this warp was
-//                     460 per chunk and the bottleneck: profiles/r1_target_rows_ws.md);
+// a V-Trace timestep for two players at 0.3 IPC = 48 ns per timestep).  Here a CTA is three warps:
+//   warp 0 (loader)   cp.async (16-byte, L2-only) of the next chunks into free ring slots; it never waits for its
+//                     own copies - cp.async.mbarrier.arrive.noinc makes each lane's copies arrive on the slot's
+//                     `full` mbarrier when they land;
 //   warp 1 (compute)  lane = (row, player): ONE sequence per lane, so a timestep is half the instructions, and
-//                     no copy instruction sits between two steps of the dependent fp32 chain.
-// Hand-over through two mbarriers per ring slot (full: bytes landed, done: results written + proxy fence).
+//                     no copy instruction sits between two steps of the dependent fp32 chain;
+//   warp 2 (storer)   streams finished slots out with 128-bit stores and hands them back (`empty`).
+// Three mbarriers per slot (full: bytes landed, done: results written, empty: slot read out).  Two earlier
+// versions are on record in profiles/: one I/O warp doing both directions (460 instructions per chunk, the
+// bottleneck) and per-row TMA bulk copies (cp.async.bulk, 256 B each: the copy engine takes ~30 cycles per
+// operation and SM, which caps such small copies at ~2 TB/s for the chip).
 // Same tiles, same Rec<> arithmetic, same bits as k_target_rows.
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
@@ -317,8 +345,10 @@ __device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* b) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* b, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+// arrive (without raising the pending count: it is part of the barrier's init count) once all cp.async issued so
+// far by this thread have landed
+__device__ __forceinline__ void mbar_arrive_on_cp_async(uint64_t* b) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(b)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
     uint32_t ok;
@@ -330,37 +360,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
             : "memory");
     } while (!ok);
 }
-// bulk copy global -> shared, completion (bytes) signalled on an mbarrier; 16-byte aligned, size % 16 == 0
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-// bulk copy shared -> global, tracked by the issuing thread's bulk async-group
-__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() {   // all but the N latest groups have finished READING shared
-    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-template <int N>
-__device__ __forceinline__ void bulk_wait() {
-    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
-}
-// generic-proxy writes to shared (STS) -> visible to the async proxy (bulk store) that reads them next
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 constexpr int WS_MAX_STAGES = 8;
 constexpr size_t WS_SMEM_CAP = 227 * 1024;             // opt-in dynamic shared memory per CTA on sm_100
-constexpr int WS_BAR_FLOATS = 2 * WS_MAX_STAGES * 2;   // 2 x 8 mbarriers of 8 bytes, in floats
+constexpr int WS_BAR_FLOATS = 3 * WS_MAX_STAGES * 2;   // 3 x 8 mbarriers of 8 bytes, in floats
 
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC>
-__global__ void __launch_bounds__(64) k_target_rows_ws(const ScanParams k, int c_alias, int ns) {
+__global__ void __launch_bounds__(96) k_target_rows_ws(const ScanParams k, int c_alias, int ns) {
     extern __shared__ __align__(16) float smem[];
     constexpr int TR = 32 / P;                       // rows per tile: one lane per (row, player)
     constexpr int RSV = RTC * P + 4;
@@ -369,8 +375,9 @@ __global__ void __launch_bounds__(64) k_target_rows_ws(const ScanParams k, int c
     const int STAGE = TR * (2 * RSV + (NEED_RHO ? (c_alias ? RSR : 2 * RSR) : 0));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* done = full + WS_MAX_STAGES;
+    uint64_t* empty = done + WS_MAX_STAGES;
     float* ring = smem + WS_BAR_FLOATS;
-    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b0 = blockIdx.x * TR;
     const int rows = min(TR, k.B - b0);
     const int n = (k.T + RTC - 1) / RTC;             // chunks, processed in order i = 0..n-1 <-> ch = n-1-i
@@ -380,68 +387,72 @@ __global__ void __launch_bounds__(64) k_target_rows_ws(const ScanParams k, int c
         for (int s = 0; s < ns; ++s) {
             mbar_init(full + s, 32);
             mbar_init(done + s, 32);
+            mbar_init(empty + s, 32);
         }
     }
     __syncthreads();
 
-    if (threadIdx.x < 32) {
-        // ---------------- I/O warp: lane = batch row ----------------
-        const bool own = lane < rows;
-        const int64_t rb = b0 + (own ? lane : 0);
-        const float* gv = k.v.p + rb * k.v.sb;
-        const float* gr = HAS_REW ? k.rew.p + rb * k.rew.sb : nullptr;
-        const float* grho = NEED_RHO ? k.rho.p + rb * k.rho.sb : nullptr;
-        const float* gc = NEED_RHO ? k.c.p + rb * k.c.sb : nullptr;
-        float* ot = k.out_t + rb * row_out;
-        float* oa = k.out_a + rb * row_out;
-        float* sv = ring + lane * RSV;                     // this row in slot 0: values / advantages
-        float* sr = ring + TR * RSV + lane * RSV;          //                     rewards / targets
-        float* srho = ring + 2 * TR * RSV + lane * RSR;
-        float* sc = srho + TR * RSR;
-        int fslot = 0;                                     // slot of the next fetch
-        auto fetch = [&](int i) {
+    if (warp == 0) {
+        // ---------------- loader ----------------
+        LaneIO<P, TR, RTC> io_v, io_r;
+        LaneIO<WR, TR, RTC> io_rho, io_c;
+        io_v.init(k.v.sb, b0, lane);
+        if (HAS_REW) io_r.init(k.rew.sb, b0, lane);
+        if (NEED_RHO) {
+            io_rho.init(k.rho.sb, b0, lane);
+            io_c.init(k.c.sb, b0, lane);
+        }
+        int slot = 0;
+        uint32_t par = 1;   // a fresh mbarrier passes a wait on the phase "before the first": all slots start empty
+        for (int i = 0; i < n; ++i) {
+            float* st = ring + slot * STAGE;
             const int t0 = (n - 1 - i) * RTC, tl = min(RTC, k.T - t0);
-            uint64_t* bar = full + fslot;
-            if (own) {
-                const uint32_t bv = tl * P * 4, br = tl * WR * 4;
-                mbar_arrive_expect_tx(bar, bv * (HAS_REW ? 2 : 1) + (NEED_RHO ? br * (c_alias ? 1 : 2) : 0));
-                const int so = fslot * STAGE;
-                bulk_g2s(sv + so, gv + t0 * P, bv, bar);
-                if (HAS_REW) bulk_g2s(sr + so, gr + t0 * P, bv, bar);
+            mbar_wait(empty + slot, par);
+            if (tl == RTC) {
+                fetch_full<P, RSV, TR, RTC>(st, k.v.p, io_v, rows, t0, lane);
+                if (HAS_REW) fetch_full<P, RSV, TR, RTC>(st + TR * RSV, k.rew.p, io_r, rows, t0, lane);
                 if (NEED_RHO) {
-                    bulk_g2s(srho + so, grho + t0 * WR, br, bar);
-                    if (!c_alias) bulk_g2s(sc + so, gc + t0 * WR, br, bar);
+                    fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV, k.rho.p, io_rho, rows, t0, lane);
+                    if (!c_alias) fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV + TR * RSR, k.c.p, io_c, rows, t0, lane);
                 }
             } else {
-                mbar_arrive(bar);
+                fetch_tile<P, RSV>(st, k.v.p, k.v.sb, b0, rows, t0, tl, lane);
+                if (HAS_REW) fetch_tile<P, RSV>(st + TR * RSV, k.rew.p, k.rew.sb, b0, rows, t0, tl, lane);
+                if (NEED_RHO) {
+                    fetch_tile<WR, RSR>(st + 2 * TR * RSV, k.rho.p, k.rho.sb, b0, rows, t0, tl, lane);
+                    if (!c_alias) fetch_tile<WR, RSR>(st + 2 * TR * RSV + TR * RSR, k.c.p, k.c.sb, b0, rows, t0, tl, lane);
+                }
             }
-            if (++fslot == ns) fslot = 0;
-        };
-        const int pre = min(ns, n);                        // every slot starts loaded
-        for (int j = 0; j < pre; ++j) fetch(j);
-        int slot = 0;
-        uint32_t par = 0;
-        for (int i = 0; i < n; ++i) {
-            mbar_wait(done + slot, par);
-            if (own) {
-                const int t0 = (n - 1 - i) * RTC, tl = min(RTC, k.T - t0);
-                const uint32_t bv = tl * P * 4;
-                const int so = slot * STAGE;
-                bulk_s2g(ot + t0 * P, sr + so, bv);
-                bulk_s2g(oa + t0 * P, sv + so, bv);
-            }
-            bulk_commit();
-            // the slot of chunk i-1 can be refilled once ITS stores have read it: leave the latest group pending
-            if (i >= 1 && i - 1 + ns < n) {
-                bulk_wait_read<1>();
-                fetch(i - 1 + ns);
-            }
+            mbar_arrive_on_cp_async(full + slot);
             if (++slot == ns) {
                 slot = 0;
                 par ^= 1;
             }
         }
-        bulk_wait<0>();
+        cp_async_wait<0>();   // nothing of this thread is in flight when the CTA retires
+    } else if (warp == 2) {
+        // ---------------- storer ----------------
+        LaneIO<P, TR, RTC> io_o;
+        io_o.init(row_out, b0, lane);
+        int slot = 0;
+        uint32_t par = 0;
+        for (int i = 0; i < n; ++i) {
+            const float* st = ring + slot * STAGE;
+            const int t0 = (n - 1 - i) * RTC, tl = min(RTC, k.T - t0);
+            mbar_wait(done + slot, par);
+            if (tl == RTC) {
+                flush_full<P, RSV, TR, RTC>(st + TR * RSV, k.out_t, io_o, rows, t0, lane);
+                flush_full<P, RSV, TR, RTC>(st, k.out_a, io_o, rows, t0, lane);
+            } else {
+                flush_tile<P, RSV>(st + TR * RSV, k.out_t, row_out, b0, rows, t0, tl, lane);
+                flush_tile<P, RSV>(st, k.out_a, row_out, b0, rows, t0, tl, lane);
+            }
+            mbar_arrive(empty + slot);   // in program order after the stores, which consumed this lane's LDS data
+            if (++slot == ns) {
+                slot = 0;
+                par ^= 1;
+            }
+        }
     } else {
         // ---------------- compute warp: lane = (row, player) ----------------
         const int r = lane / P, p = lane % P;
@@ -527,7 +538,6 @@ __global__ void __launch_bounds__(64) k_target_rows_ws(const ScanParams k, int c
                 }
                 if (q == 0) compute_group(ga, 0, std::false_type{});
             }
-            fence_proxy_async();
             mbar_arrive(done + slot);
             if (++slot == ns) {
                 slot = 0;
@@ -581,7 +591,7 @@ int launch_shape(const ScanParams& k, cudaStream_t st) {
     return b200rl_check_launch("k_target_rows");
 }
 
-// Warp-specialised launch (k_target_rows_ws): one CTA of two warps per tile of 32/P rows, ring as deep as the
+// Warp-specialised launch (k_target_rows_ws): one CTA of three warps per tile of 32/P rows, ring as deep as the
 // shared memory allows for the number of CTAs an SM has to hold.
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC>
 int launch_ws(const ScanParams& k, cudaStream_t st) {
@@ -605,36 +615,31 @@ int launch_ws(const ScanParams& k, cudaStream_t st) {
     const int want = (ntiles + sms - 1) / sms;   // CTAs an SM holds when the whole grid is resident
     const char* ns_e = getenv("B200RL_TARGET_WS_STAGES");
     const int ns_env = ns_e ? atoi(ns_e) : 0;
-    int ns = 3;
+    int ns = 2;
     while (ns < WS_MAX_STAGES && (size_t)want * (BAR + (ns + 1) * stage + 1024) <= (size_t)220 * 1024) ++ns;
     if (ns_env >= 2 && ns_env <= WS_MAX_STAGES) ns = ns_env;
     while (ns > 2 && BAR + ns * stage > WS_SMEM_CAP) --ns;
-    kern<<<ntiles, 64, BAR + ns * stage, st>>>(k, alias ? 1 : 0, ns);
+    kern<<<ntiles, 96, BAR + ns * stage, st>>>(k, alias ? 1 : 0, ns);
     return b200rl_check_launch("k_target_rows_ws");
 }
 
-// B200RL_TARGET_WS=0 / 1 forces the one-warp / warp-specialised kernel for A/B measurements; by default the
-// warp-specialised one takes the launches with few tiles (see ws_tiles_max), where the sequential depth of a warp
-// and not HBM is the bound.
-// (read at every call, so that a test can switch kernels inside one process)
-inline int ws_mode() {
-    const char* e = getenv("B200RL_TARGET_WS");
-    return e ? atoi(e) : -1;
-}
-inline int ws_tiles_max() {
-    const char* e = getenv("B200RL_TARGET_WS_TILES");
-    return e ? atoi(e) : 1184;
+// Chunk width of the warp-specialised kernel: 256 B per row and fetch up to B200RL_TARGET_WS_WIDE_ROWS batch rows
+// (more chunks in flight per CTA while few CTAs share an SM), 512 B beyond (measured at B = 65,536: +3-9 % at
+// T = 200, +2-4 % at T = 1024; at B = 16,384 and T = 200 the wide chunks are 15 % slower).
+// B200RL_TARGET_WS_ROW=256 / 512 forces either (read at every call, so that a test can cover both in one process).
+inline int ws_row_bytes(int B) {
+    const char* e = getenv("B200RL_TARGET_WS_ROW");
+    if (e) return atoi(e) >= 512 ? 512 : 256;
+    const char* w = getenv("B200RL_TARGET_WS_WIDE_ROWS");
+    return B >= (w ? atoi(w) : 32768) ? 512 : 256;
 }
 
-// long rows: 16-row tiles, 256 B per row per fetch (32 steps at P = 2, 64 at P = 1); rows of <= 64 steps: 32 x 16
+// long rows: the warp-specialised kernel (16-row tiles at P = 2); rows of <= 64 steps: one warp per 32 x 16 tile
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
 int launch_rows(const ScanParams& k, cudaStream_t st) {
     if (k.T > B200RL_SHORT_T) {
-        const int wm = ws_mode();
-        const int ws_tiles = (k.B + 32 / P - 1) / (32 / P);
-        if (wm == 1 || (wm < 0 && ws_tiles <= ws_tiles_max()))
-            return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P>(k, st);
-        return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 16, 64 / P>(k, st);
+        if (ws_row_bytes(k.B) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P>(k, st);
+        return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P>(k, st);
     }
     return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 32, 16>(k, st);
 }

@@ -95,30 +95,28 @@ def test_cs_is_rhos_same_tensor(B, T, P, rpp, vt, pt):
                                        (4096, 1024, 2, False), (17, 68, 2, False)])
 @pytest.mark.parametrize("vt,pt", [('TD', 'TD'), ('UPGO', 'UPGO'), ('VTRACE', 'VTRACE'), ('VTRACE', 'UPGO')])
 @pytest.mark.parametrize("head", ['value', 'return'])
-def test_long_rows_both_kernels(monkeypatch, B, T, P, rpp, vt, pt, head):
-    """Rows longer than 64 steps have two kernels: one warp per tile (many tiles) and the warp-specialised
-    I/O + compute pair (few tiles).  B200RL_TARGET_WS forces either; both must give the oracle's bits, with
-    ragged last tiles, a partial first chunk (T % 32 != 0), per-player rhos, P = 1 and cs aliasing rhos."""
+def test_long_rows_ws_kernel(monkeypatch, B, T, P, rpp, vt, pt, head):
+    """Rows longer than 64 steps run in the warp-specialised kernel (loader / compute / storer warps, mbarrier
+    ring).  Both chunk widths and several ring depths must give the oracle's bits, with ragged last tiles, a
+    partial first chunk (T % chunk != 0), per-player rhos, P = 1 and cs aliasing rhos."""
     from handyrl_b200.losses import compute_target_pair
     d = target_inputs(B, T, P, head, rpp, seed=B + T + 7)
     rt, _ = targets_np.compute_target(vt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['cs'])
     _, ra = targets_np.compute_target(pt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['cs'])
     g = _cuda(d)
     a = (g['values'], g['returns'], g['rewards'], g['lmb'], g['gamma'])
-    for ws in ('0', '1'):
+    for row in ('256', '512'):
         for stages in ('2', '5'):
-            monkeypatch.setenv('B200RL_TARGET_WS', ws)
+            monkeypatch.setenv('B200RL_TARGET_WS_ROW', row)
             monkeypatch.setenv('B200RL_TARGET_WS_STAGES', stages)
             t1, a1 = compute_target_pair(vt, pt, *a, g['rhos'], g['cs'])
             _close(t1, np.asarray(rt))
             _close(a1, np.asarray(ra))
+    monkeypatch.delenv('B200RL_TARGET_WS_ROW')
+    monkeypatch.delenv('B200RL_TARGET_WS_STAGES')
     if 'VTRACE' in (vt, pt):
-        d2 = dict(d)
-        d2['cs'] = d['rhos']
         rt2, _ = targets_np.compute_target(vt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['rhos'])
         _, ra2 = targets_np.compute_target(pt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['rhos'])
-        monkeypatch.setenv('B200RL_TARGET_WS', '1')
-        monkeypatch.delenv('B200RL_TARGET_WS_STAGES')
         t1, a1 = compute_target_pair(vt, pt, *a, g['rhos'], g['rhos'])
         _close(t1, np.asarray(rt2))
         _close(a1, np.asarray(ra2))
