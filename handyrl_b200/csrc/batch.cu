@@ -59,7 +59,7 @@ k_step_record(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, c
         atomicAdd(&counters[1 + wincode], 1ull);
         if (ep_table) {
             unsigned long long idx = atomicAdd(&counters[5], 1ull);
-            int32_t* e = ep_table + (int64_t)(idx % (unsigned long long)E) * 4;
+            int32_t* e = ep_table + (int64_t)ring_mod(idx, (uint64_t)E) * 4;
             e[0] = (int32_t)i;
             e[1] = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
             e[2] = (int32_t)(uint32_t)it;
@@ -145,7 +145,7 @@ k_sample_record(uint32_t* state, int64_t N, const float* __restrict__ logits, co
             atomicAdd(&counters[1 + wincode], 1ull);
             if (ep_table) {
                 unsigned long long idx = atomicAdd(&counters[5], 1ull);
-                int32_t* e = ep_table + (int64_t)(idx % (unsigned long long)E) * 4;
+                int32_t* e = ep_table + (int64_t)ring_mod(idx, (uint64_t)E) * 4;
                 e[0] = (int32_t)i;
                 e[1] = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
                 e[2] = (int32_t)(uint32_t)it;
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
                 const bool is_turn = parallel || pl == tp;
                 const bool observed = is_turn || p.obs_all;
                 float v = 0.f;
-                if (observed && p.values) v = p.values[((int64_t)(it % (uint64_t)p.D) * p.N + slot) * 2 + pl];
+                if (observed && p.values) v = p.values[((int64_t)ring_mod(it, (uint64_t)p.D) * p.N + slot) * 2 + pl];
                 val[q] = v;
                 rew[q] = G::HAS_REWARD ? G::reward(s) : 0.f;
                 const int left = total - (stt + t);
@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(BLK) k_policy_from_logits(const BatchParams p)
     any = __any_sync(0xffffffffu, any);
     const bool live = t < w[3] && any;
     const uint64_t it = ((uint64_t)(uint32_t)w[1] | ((uint64_t)(uint32_t)w[2] << 32)) + (uint64_t)t;
-    const float* lg = p.logits + ((int64_t)(it % (uint64_t)p.D) * p.N + w[0]) * G::A;
+    const float* lg = p.logits + ((int64_t)ring_mod(it, (uint64_t)p.D) * p.N + w[0]) * G::A;
     for (int a = lane; a < G::A; a += 32)
         p.policy[r * G::A + a] = live ? __fsub_rn(lg[a], p.amask[r * G::A + a]) : 0.f;
 }

@@ -59,9 +59,15 @@ __device__ __forceinline__ uint4 ld_stream_u4(const uint4* p) {
 // make_batch reads them as one coalesced 1 KB request (the ply-major [D][N] layout cost make_batch 14 %: 2 M
 // isolated 32-byte sector reads, 4x read amplification).  The rollout pays for it with strided writes, which it
 // combines into full 128-byte lines (4 plies) through shared memory.  One 256-bit access per record.
+// x mod m for ring indices: rings are normally sized to powers of two, where the 64-bit remainder (~70
+// instructions, 13 % of the TicTacToe rollout's instruction stream before this) is one AND.
+__device__ __forceinline__ uint64_t ring_mod(uint64_t x, uint64_t m) {
+    return (m & (m - 1)) == 0 ? (x & (m - 1)) : (x % m);
+}
+
 __device__ __forceinline__ void st_record(void* traj, int64_t D, int64_t N, uint64_t it, int64_t i,
                                           const uint32_t (&r)[8]) {
-    uint32_t* p = reinterpret_cast<uint32_t*>(traj) + (i * D + (int64_t)(it % (uint64_t)D)) * 8;
+    uint32_t* p = reinterpret_cast<uint32_t*>(traj) + (i * D + (int64_t)ring_mod(it, (uint64_t)D)) * 8;
     asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]),
                  "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
                  : "memory");
@@ -69,7 +75,7 @@ __device__ __forceinline__ void st_record(void* traj, int64_t D, int64_t N, uint
 
 __device__ __forceinline__ void ld_record(const void* traj, int64_t D, int64_t N, uint64_t it, int64_t i,
                                           uint32_t (&r)[8]) {
-    const uint32_t* p = reinterpret_cast<const uint32_t*>(traj) + (i * D + (int64_t)(it % (uint64_t)D)) * 8;
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(traj) + (i * D + (int64_t)ring_mod(it, (uint64_t)D)) * 8;
     asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "l"(p));

@@ -122,6 +122,18 @@ __device__ __forceinline__ void emit_flat_f32(const uint32_t* __restrict__ flat,
     // lane q always reads nibble (q & 7) of word (q >> 3) + 4*j: constant shift, constant address stride
     const int sh = (lane & 7) << 2;
     const uint32_t* fw = flat + (lane >> 3);
+    if (NB * 8 <= 256 && rows <= 32) {
+        // small tiles (TicTacToe, one row per lane: 216 and 72 float4): fully unrolled, constant word offsets,
+        // predicated stores; make_batch's two-player cells (up to 64 rows) take the general loops below
+        constexpr int IT = (NB * 8 + 31) / 32;
+#pragma unroll
+        for (int u = 0; u < IT; ++u) {
+            const int qq = lane + 32 * u;
+            if (qq < n4) st_stream_f4(o4 + qq, nibble_expand(fw[4 * u] >> sh, tbl, v0, v1));
+        }
+        for (int e = (n4 << 2) + lane; e < total; e += 32) out_tile[e] = ((flat[e >> 5] >> (e & 31)) & 1u) ? v1 : v0;
+        return;
+    }
     int q = lane;
 #pragma unroll 1
     for (; q + 96 < n4; q += 128) {

@@ -214,22 +214,46 @@ k_step_observe(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, 
     emit_views<G>(stage, warp, s, valid, B200RL_VIEW_TURN, g0, ng, lane, out_main, out_scalar, out_amask, nullptr);
 }
 
-// k-th (0-based) set bit of an LW-word mask
-template <int LW>
+// position of the k-th (0-based) set bit of x, k < popc(x): branch-free binary search on popcounts (the
+// clear-lowest-bit loop it replaces diverged inside the warp and was 8 % of the TicTacToe rollout's instructions)
+template <int BITS>
+__device__ __forceinline__ int select_bit(uint32_t x, int k) {
+    int pos = 0;
+#pragma unroll
+    for (int h = 16; h >= 1; h >>= 1) {
+        if (h < BITS) {
+            const int c = __popc(x & ((1u << h) - 1u));
+            const bool up = k >= c;
+            k -= up ? c : 0;
+            pos += up ? h : 0;
+            x >>= up ? h : 0;
+        }
+    }
+    return pos;
+}
+
+// k-th (0-based) set bit of an LW-word mask of NBITS valid bits
+template <int LW, int NBITS>
 __device__ __forceinline__ int kth_set_bit(const uint32_t (&m)[LW], int k) {
+    if (LW == 1) return select_bit<(NBITS <= 16 ? 16 : 32)>(m[0], k);
+    // find the word, then the bit inside it
     int base = 0;
+    uint32_t x = m[0];
+    bool found = false;
 #pragma unroll
     for (int w = 0; w < LW; ++w) {
         const int c = __popc(m[w]);
-        if (k < c) {
-            uint32_t x = m[w];
-            for (int j = 0; j < k; ++j) x &= x - 1;
-            return base + __ffs(x) - 1;
+        if (!found) {
+            if (k < c) {
+                found = true;
+                x = m[w];
+                base = 32 * w;
+            } else {
+                k -= c;
+            }
         }
-        k -= c;
-        base += 32;
     }
-    return -1;
+    return found ? base + select_bit<32>(x, k) : -1;
 }
 
 struct RolloutParams {
@@ -261,6 +285,19 @@ __device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) 
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+constexpr int EP_BUF = 64;   // finished-episode rows buffered per warp before one append to the table
+
+// append n buffered rows to the episode-table ring: one atomic on the head, then coalesced row stores
+__device__ __forceinline__ void ep_flush(const RolloutParams& p, const int4* buf, int n, int lane) {
+    __syncwarp();
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(&p.counters[5], (unsigned long long)n);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    for (int r = lane; r < n; r += 32)
+        *reinterpret_cast<int4*>(p.ep_table + (int64_t)ring_mod(base + (unsigned long long)r, (uint64_t)p.E) * 4) = buf[r];
+    __syncwarp();
+}
+
 // Persistent self-play with the epoch-0 policy (uniform over legal actions ==
 // RandomModel's zero logits, handyrl/model.py:58-64): every ply emits the reference-format moment data
 // (observation, action_mask, action) and/or a 32-byte compact trajectory record.
@@ -287,6 +324,8 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
     unsigned int n_ep = 0, n_w0 = 0, n_w1 = 0, n_dr = 0;
     unsigned long long n_steps = 0;
     uint32_t rec_fill = 0;   // bit q: rec_stage[..][q] holds the record of the current 4-ply group
+    __shared__ int4 ep_buf[WARPS][EP_BUF];
+    int ep_n = 0;            // rows waiting in ep_buf[warp] (warp-uniform)
 
     for (;;) {
         unsigned int tk = 0;
@@ -332,10 +371,10 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                 for (int w = 0; w < G::LW; ++w) cnt += __popc(lm[w]);
                 const uint32_t r = b200rl_rand32(p.seed, stream_id, it);
                 const int kk = (int)__umulhi(r, (uint32_t)cnt);
-                action = kth_set_bit<G::LW>(lm, kk);
+                action = kth_set_bit<G::LW, G::A>(lm, kk);
                 selp = (int)((r >> 7) & 1);  // ParallelTicTacToe: which player's move lands
             }
-            const int64_t wv = p.waves > 0 ? (int64_t)(it % (uint64_t)p.waves) : 0;
+            const int64_t wv = p.waves > 0 ? (int64_t)ring_mod(it, (uint64_t)p.waves) : 0;
             if (p.out_main || p.out_amask || p.out_scalar) {
                 emit_views<G>(stage, warp, s, valid, B200RL_VIEW_TURN, g0, ng, lane,
                               p.out_main ? p.out_main + wv * p.N * G::OBITS : nullptr,
@@ -370,23 +409,26 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                 }
             }
             if (p.ep_table) {
-                // episode-table append, one atomic per warp and ply: TicTacToe finishes ~4 of a warp's 32 games every
-                // ply, and 3 G same-address atomics per second was what bounded its rollout
+                // episode-table append: finished games' rows are collected in a per-warp shared buffer and appended
+                // EP_BUF at a time (one atomic on the table head + coalesced 16-byte row stores).  TicTacToe finishes
+                // ~4 of a warp's 32 games every ply; waiting for one returning global atomic per ply was 12 % of that
+                // rollout's stall samples, and before that 3 G same-address atomics per second were its bound.
                 const unsigned int fin = __ballot_sync(0xffffffffu, term);
                 if (fin) {
-                    const int leader = __ffs(fin) - 1;
-                    unsigned long long base = 0;
-                    if (lane == leader) base = atomicAdd(&p.counters[5], (unsigned long long)__popc(fin));
-                    base = __shfl_sync(0xffffffffu, base, leader);
+                    const int nf = __popc(fin);
+                    if (ep_n + nf > EP_BUF) {
+                        ep_flush(p, ep_buf[warp], ep_n, lane);
+                        ep_n = 0;
+                    }
                     if (term) {
-                        const unsigned long long idx = base + (unsigned long long)__popc(fin & ((1u << lane) - 1u));
                         int4 row;
                         row.x = (int32_t)i;
                         row.y = (int32_t)((uint32_t)G::steps(s) | (wincode << 16));
                         row.z = (int32_t)(uint32_t)it;
                         row.w = (int32_t)(uint32_t)(it >> 32);
-                        *reinterpret_cast<int4*>(p.ep_table + (int64_t)(idx % (unsigned long long)p.E) * 4) = row;
+                        ep_buf[warp][ep_n + __popc(fin & ((1u << lane) - 1u))] = row;
                     }
+                    ep_n += nf;
                 }
             }
             if (p.traj) {
@@ -411,6 +453,10 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                     __syncwarp();
                 }
             }
+        }
+        if (p.ep_table && ep_n) {
+            ep_flush(p, ep_buf[warp], ep_n, lane);
+            ep_n = 0;
         }
         if (valid) G::store(p.state, p.N, i, s);
         n_steps += (unsigned long long)ng * (unsigned long long)(k_end - k_begin);
