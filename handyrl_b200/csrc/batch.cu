@@ -424,19 +424,17 @@ __host__ __device__ inline void select_one_window(const int32_t* ep_table, int64
     }
     const int64_t n_draw = L < maximum_episodes ? L : maximum_episodes;
     int32_t slot = 0, steps = 1, win = 3;
-    uint64_t end_it = 0;
-    uint32_t r2 = 0, r3 = 0;
+    uint64_t end_it = 0, c = draw0;
+    const bool e_pow2 = (E & (E - 1)) == 0;
     for (int tr = 0; tr < 64; ++tr) {
-        const uint64_t c = draw0 + 4ull * (uint64_t)tr;
+        c = draw0 + 4ull * (uint64_t)tr;
         const uint32_t r0 = b200rl_rand32(seed, (uint64_t)b, c), r1 = b200rl_rand32(seed, (uint64_t)b, c + 1);
-        r2 = b200rl_rand32(seed, (uint64_t)b, c + 2);
-        r3 = b200rl_rand32(seed, (uint64_t)b, c + 3);
         int64_t ep_idx = (int64_t)(((unsigned long long)r0 * (unsigned long long)n_draw) >> 32);  // train.py:286
         const double accept = 1.0 - (double)(L - 1 - ep_idx) / (double)maximum_episodes;         // train.py:287
         const bool last_try = tr == 63;
         if (last_try) ep_idx = L - 1;
-        const int32_t* e = ep_table + (int64_t)((cursor - (unsigned long long)L + (unsigned long long)ep_idx) %
-                                                 (unsigned long long)E) * 4;
+        const unsigned long long pos = cursor - (unsigned long long)L + (unsigned long long)ep_idx;
+        const int32_t* e = ep_table + (int64_t)(e_pow2 ? (pos & (unsigned long long)(E - 1)) : (pos % (unsigned long long)E)) * 4;
         slot = e[0];
         steps = e[1] & 0xFFFF;
         win = (e[1] >> 16) & 3;
@@ -444,6 +442,8 @@ __host__ __device__ inline void select_one_window(const int32_t* ep_table, int64
         const bool alive = it_now - (end_it + 1 - (uint64_t)steps) <= (uint64_t)D;
         if (last_try || (alive && (double)r1 * (1.0 / 4294967296.0) < accept)) break;  // train.py:288
     }
+    // the window-start and solo-player draws of the accepted try (rejected tries never needed theirs)
+    const uint32_t r2 = b200rl_rand32(seed, (uint64_t)b, c + 2), r3 = b200rl_rand32(seed, (uint64_t)b, c + 3);
     const int cand = 1 + (steps - forward_steps > 0 ? steps - forward_steps : 0);         // train.py:291
     const int st = (int)(((unsigned long long)r2 * (unsigned long long)cand) >> 32);       // train.py:292
     const int ed = st + forward_steps < steps ? st + forward_steps : steps;               // train.py:293
@@ -630,10 +630,27 @@ extern "C" int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t 
                    "select_windows_host: bad E/D/maximum_episodes/forward_steps/B");
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 64) n_threads = 64;
+    // The table (16 B per finished episode, up to E rows) does not fit the host caches and every try of the
+    // rejection sampling reads one random row: the rows of the first two tries of the next PF windows are
+    // prefetched while the current block is drawn (the draws are counter-based, so they can be recomputed).
+    int64_t Lh = (int64_t)(cursor < (unsigned long long)E ? cursor : (unsigned long long)E);
+    if (Lh > maximum_episodes) Lh = maximum_episodes;
+    auto prefetch = [&](int64_t b) {
+        if (Lh <= 0) return;
+        for (int tr = 0; tr < 2; ++tr) {
+            const uint32_t r0 = b200rl_rand32(seed, (uint64_t)b, draw0 + 4ull * (uint64_t)tr);
+            const unsigned long long pos = cursor - (unsigned long long)Lh + (((unsigned long long)r0 * (unsigned long long)Lh) >> 32);
+            __builtin_prefetch(ep_table_host + (int64_t)(pos % (unsigned long long)E) * 4);
+        }
+    };
+    constexpr int64_t PF = 16;
     auto work = [&](int64_t lo, int64_t hi) {
-        for (int64_t b = lo; b < hi; ++b)
+        for (int64_t b = lo; b < hi && b < lo + PF; ++b) prefetch(b);
+        for (int64_t b = lo; b < hi; ++b) {
+            if (b + PF < hi) prefetch(b + PF);
             select_one_window(ep_table_host, E, cursor, maximum_episodes, (int)forward_steps, seed, draw0, it_now, D, b,
                               out_windows_host + b * 8);
+        }
     };
     if (n_threads == 1 || B < 4096) {
         work(0, B);
