@@ -229,7 +229,7 @@ def main():
     import torch
     import torch.distributed as dist
     from handyrl_b200.generation import BatchGenerator, HostReplayIndex
-    from handyrl_b200.losses import compute_target_pair
+    from handyrl_b200.losses import compute_target_heads
     from handyrl_b200.train import make_batch_windows
 
     torch.cuda.set_device(local_rank)
@@ -272,8 +272,8 @@ def main():
         rec(2)
         v, vr, rho, c = tsets[k % NSETS]
         # train.py:245-253 with value_target UPGO / policy_target VTRACE: targets of the first, advantages of the second
-        t1 = compute_target_pair("UPGO", "VTRACE", v, batch["outcome"], None, 0.7, 1.0, rho, c)
-        t2 = compute_target_pair("UPGO", "VTRACE", vr, batch["return"], batch["reward"], 0.7, 0.8, rho, c)
+        t1, t2 = compute_target_heads("UPGO", "VTRACE", [(v, batch["outcome"], None, 1.0),
+                                                          (vr, batch["return"], batch["reward"], 0.8)], 0.7, rho, c)
         rec(3)
         return t1, t2
 
@@ -332,8 +332,8 @@ def main():
         def step_tail(k, win):
             state["batch"] = batch = make_batch_windows(gen.store, win, TRAIN_ARGS, out=state["batch"])
             v, vr, rho, c = tsets[k % NSETS]
-            t1 = compute_target_pair("UPGO", "VTRACE", v, batch["outcome"], None, 0.7, 1.0, rho, c)
-            t2 = compute_target_pair("UPGO", "VTRACE", vr, batch["return"], batch["reward"], 0.7, 0.8, rho, c)
+            t1, t2 = compute_target_heads("UPGO", "VTRACE", [(v, batch["outcome"], None, 1.0),
+                                                              (vr, batch["return"], batch["reward"], 0.8)], 0.7, rho, c)
             return t1, t2
 
         e2e_evs = []
@@ -412,7 +412,7 @@ def main():
                                                              "make_batch_targets", "summary_d2h"))},
                "note": "per step: BatchGenerator.rollout; D2H of the counters and the new finished-episode rows; "
                        "HostReplayIndex.select (b200rl_select_windows_host, replay index on the host) overlapped with the GPU; pinned H2D of the "
-                       "windows on a copy stream (event-ordered) beside the kernels; make_batch_windows; compute_target_pair x2; D2H of the target summary. Moments stay in "
+                       "windows on a copy stream (event-ordered) beside the kernels; make_batch_windows; compute_target_heads (value + return head, one launch); D2H of the target summary. Moments stay in "
                        "HBM (the trajectory ring is the replay buffer). Wall clock incl. all host work."}
 
         # the same self-play driven ply by ply from HOST buffers (reference Environment-style stepping: actions
@@ -473,7 +473,7 @@ def main():
                             "env-step"),
             "make_batch": roof("k_select_windows + k_make_batch<Geister>", BYTES_PER_BATCH_CELL * B * T, batch_ms,
                                BYTES_PER_BATCH_CELL, "(b,t) batch cell"),
-            "targets": roof("k_target_rows<UPGO,VTRACE> x2 (value + return head)", BYTES_PER_TARGET_PAIR * B * T * P,
+            "targets": roof("k_target_rows2<UPGO,VTRACE> (value + return head, one launch)", BYTES_PER_TARGET_PAIR * B * T * P,
                             tgt_ms, BYTES_PER_TARGET_PAIR, "(b,t,p) element, both heads"),
         }
         dominant = max(roofs, key=lambda k: roofs[k]["avg_ms"])
@@ -493,7 +493,7 @@ def main():
             "phases": {"rollout_ms": roll_ms, "make_batch_ms": batch_ms, "targets_ms": tgt_ms,
                        "env_steps_per_sec_rollout_only": env_steps_per_step / (roll_ms * 1e-3)},
             "roofline": roofs[dominant], "rooflines": roofs,
-            "clocks": clocks, "e2e": e2e, "gpu_launches": 5 * args.steps,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": 4 * args.steps,
         }
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline()

@@ -24,6 +24,16 @@ class B200RLError(RuntimeError):
     pass
 
 
+class TargetHead(ctypes.Structure):
+    """b200rl_target_head (include/b200rl.h)."""
+    _fields_ = ([("values", c_ptr), ("v_sb", c_i64), ("v_st", c_i64), ("v_sp", c_i64),
+                 ("boot", c_ptr), ("boot_sb", c_i64), ("boot_sp", c_i64),
+                 ("rewards", c_ptr), ("r_sb", c_i64), ("r_st", c_i64), ("r_sp", c_i64),
+                 ("rhos", c_ptr), ("rho_sb", c_i64), ("rho_st", c_i64), ("rho_sp", c_i64),
+                 ("cs", c_ptr), ("c_sb", c_i64), ("c_st", c_i64), ("c_sp", c_i64),
+                 ("out_targets", c_ptr), ("out_adv", c_ptr), ("gamma", c_dbl)])
+
+
 def _view3():
     return [c_ptr, c_i64, c_i64, c_i64]
 
@@ -43,6 +53,7 @@ SIGNATURES = {
     "b200rl_version": [],
     "b200rl_target_scan": [c_int] + _SCAN_TAIL,
     "b200rl_target_scan_fused": [c_int, c_int] + _SCAN_TAIL,
+    "b200rl_target_scan_heads": [c_int, c_int, c_ptr, c_int, c_i64, c_i64, c_i64, c_dbl, c_ptr],
     "b200rl_target_mc": _view3() + _view3() + [c_ptr, c_i64, c_i64, c_i64, c_ptr],
     "b200rl_env_state_bytes": [c_int],
     "b200rl_env_dims": [c_int, c_ptr],

@@ -112,3 +112,5 @@ __device__ __forceinline__ void rec_step(Rec<MODE>& rec, bool last, float v, flo
 // Row-per-thread fast path (target_rows.cu).  Returns -1 when the layout is not eligible
 // (caller falls back to the generic kernel), else a b200rl status.
 int b200rl_launch_target_rows(int mt, int ma, const ScanParams& k, bool has_rew, cudaStream_t st);
+// Two heads (same B, T, P; rows of <= 64 steps) in one launch; -1 when not eligible.
+int b200rl_launch_target_rows2(int mt, int ma, const ScanParams& k0, const ScanParams& k1, cudaStream_t st);

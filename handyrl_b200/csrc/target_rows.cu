@@ -179,9 +179,13 @@ __device__ __forceinline__ void scan_group(const float (&v)[4 * P], const float 
 
 // ns = ring depth (2..4 stages): 2 when the grid fills the SMs (more resident warps hide the latency better than
 // deeper rings), up to 4 when there are few tiles and each warp has to cover the DRAM latency on its own.
-template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int TR, int RTC>
-__global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntiles, int c_alias, int ns) {
+// DUAL: the tile belongs to one of two heads launched together (k_target_rows2); whether that head has rewards
+// is then a run-time property of its ScanParams (a head without rewards scans with r = 0, like HAS_REW = false).
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int TR, int RTC, bool DUAL>
+__device__ __forceinline__ void target_rows_tiles(const ScanParams& k, int tile0, int tile_step, int ntiles, int c_alias,
+                                                  int ns) {
     extern __shared__ __align__(16) float smem[];
+    const bool rew_rt = !DUAL || k.rew.p != nullptr;
     constexpr int RSV = RTC * P + 4;                 // row stride of the value / reward tiles (floats)
     constexpr int WR = RHO_PP ? P : 1;               // floats per timestep of rho / c
     constexpr int RSR = RTC * WR + 4;
@@ -190,7 +194,7 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
     const int lane = threadIdx.x;
     const int64_t row_out = (int64_t)k.T * P;
 
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < ntiles; tile += tile_step) {
         const int b0 = tile * TR;
         const int rows = min(TR, k.B - b0);
         const bool active = lane < rows;
@@ -206,7 +210,7 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
         LaneIO<WR, TR, RTC> io_rho, io_c;
         io_v.init(k.v.sb, b0, lane);
         io_o.init(row_out, b0, lane);
-        if (HAS_REW) io_r.init(k.rew.sb, b0, lane);
+        if (HAS_REW && rew_rt) io_r.init(k.rew.sb, b0, lane);
         if (NEED_RHO) {
             io_rho.init(k.rho.sb, b0, lane);
             io_c.init(k.c.sb, b0, lane);
@@ -217,14 +221,14 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
                 const int t0 = ch * RTC, tl = min(RTC, k.T - t0);
                 if (tl == RTC) {
                     fetch_full<P, RSV, TR, RTC>(st, k.v.p, io_v, rows, t0, lane);
-                    if (HAS_REW) fetch_full<P, RSV, TR, RTC>(st + TR * RSV, k.rew.p, io_r, rows, t0, lane);
+                    if (HAS_REW && rew_rt) fetch_full<P, RSV, TR, RTC>(st + TR * RSV, k.rew.p, io_r, rows, t0, lane);
                     if (NEED_RHO) {
                         fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV, k.rho.p, io_rho, rows, t0, lane);
                         if (!c_alias) fetch_full<WR, RSR, TR, RTC>(st + 2 * TR * RSV + TR * RSR, k.c.p, io_c, rows, t0, lane);
                     }
                 } else {
                     fetch_tile<P, RSV>(st, k.v.p, k.v.sb, b0, rows, t0, tl, lane);
-                    if (HAS_REW) fetch_tile<P, RSV>(st + TR * RSV, k.rew.p, k.rew.sb, b0, rows, t0, tl, lane);
+                    if (HAS_REW && rew_rt) fetch_tile<P, RSV>(st + TR * RSV, k.rew.p, k.rew.sb, b0, rows, t0, tl, lane);
                     if (NEED_RHO) {
                         fetch_tile<WR, RSR>(st + 2 * TR * RSV, k.rho.p, k.rho.sb, b0, rows, t0, tl, lane);
                         if (!c_alias) fetch_tile<WR, RSR>(st + 2 * TR * RSV + TR * RSR, k.c.p, k.c.sb, b0, rows, t0, tl, lane);
@@ -254,7 +258,10 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
 #pragma unroll
                     for (int u = 0; u < P; ++u) {
                         g.v[u] = *reinterpret_cast<const float4*>(pv + q * 4 * P + 4 * u);
-                        if (HAS_REW) g.r[u] = *reinterpret_cast<const float4*>(pr + q * 4 * P + 4 * u);
+                        if (HAS_REW) {
+                            if (rew_rt) g.r[u] = *reinterpret_cast<const float4*>(pr + q * 4 * P + 4 * u);
+                            else g.r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
                     }
                     if (NEED_RHO) {
 #pragma unroll
@@ -322,6 +329,22 @@ __global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntil
     }
 }
 
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int TR, int RTC>
+__global__ void __launch_bounds__(32) k_target_rows(const ScanParams k, int ntiles, int c_alias, int ns) {
+    target_rows_tiles<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, TR, RTC, false>(k, blockIdx.x, gridDim.x, ntiles, c_alias, ns);
+}
+
+// Two heads of one loss (value head: outcome bootstrap, no rewards, gamma 1; return head: rewards, gamma) in ONE
+// launch: CTA 2j is tile j of head 0, CTA 2j+1 tile j of head 1.  At B = 65,536, T = 32 each head is a 13-16 us
+// kernel; two launches cost their ramp-up and drain twice (bench.py: 0.042 ms for 0.029 ms of kernel time).
+struct ScanParams2 {
+    ScanParams h[2];
+};
+template <int MT, int MA, int P, bool NEED_RHO, bool RHO_PP, int TR, int RTC>
+__global__ void __launch_bounds__(32) k_target_rows2(const ScanParams2 kk, int ntiles, int c_alias, int ns) {
+    target_rows_tiles<MT, MA, P, true, NEED_RHO, RHO_PP, TR, RTC, true>(kk.h[blockIdx.x & 1], blockIdx.x >> 1, ntiles,
+                                                                        ntiles, c_alias, ns);
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Warp-specialised variant for FEW tiles (small B, long rows): the recursion is then bounded by the sequential
@@ -591,6 +614,38 @@ int launch_shape(const ScanParams& k, cudaStream_t st) {
     return b200rl_check_launch("k_target_rows");
 }
 
+// Two heads in one launch (short rows only: for longer rows one head already fills the machine for > 70 us).
+template <int MT, int MA, int P, bool NEED_RHO, bool RHO_PP>
+int launch_dual(const ScanParams& k0, const ScanParams& k1, cudaStream_t st) {
+    constexpr int TR = 32, RTC = 16;
+    constexpr int RSV = RTC * P + 4;
+    constexpr int RSR = RTC * (RHO_PP ? P : 1) + 4;
+    auto is_alias = [](const ScanParams& k) {
+        return NEED_RHO && k.c.p == k.rho.p && k.c.sb == k.rho.sb && k.c.st == k.rho.st && k.c.sp == k.rho.sp;
+    };
+    const bool alias = is_alias(k0);
+    if (alias != is_alias(k1)) return -1;
+    const int stage = TR * (2 * RSV + (NEED_RHO ? (alias ? RSR : 2 * RSR) : 0));
+    auto kern = k_target_rows2<MT, MA, P, NEED_RHO, RHO_PP, TR, RTC>;
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        constexpr size_t SMEM_MAX = (size_t)4 * TR * (2 * RSV + 2 * RSR) * sizeof(float);
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
+    }
+    const int ntiles = (k0.B + TR - 1) / TR;
+    const int want = (2 * ntiles + sms - 1) / sms;
+    int ns = NSTAGE;
+    while (ns < 4 && (size_t)want * (ns + 1) * stage * sizeof(float) <= (size_t)200 * 1024) ++ns;
+    ScanParams2 kk;
+    kk.h[0] = k0;
+    kk.h[1] = k1;
+    kern<<<2 * ntiles, 32, (size_t)ns * stage * sizeof(float), st>>>(kk, ntiles, alias ? 1 : 0, ns);
+    return b200rl_check_launch("k_target_rows2");
+}
+
 // Warp-specialised launch (k_target_rows_ws): one CTA of three warps per tile of 32/P rows, ring as deep as the
 // shared memory allows for the number of CTAs an SM has to hold.
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC>
@@ -682,6 +737,48 @@ int b200rl_launch_target_rows(int mt, int ma, const ScanParams& k, bool has_rew,
 #define CASE(A, B_)                                                                      \
     if (mt == A && ma == B_)                                                             \
         return P == 1 ? launch_rows_p<A, B_, 1>(k, has_rew, rho_pp, st) : launch_rows_p<A, B_, 2>(k, has_rew, rho_pp, st);
+    CASE(B200RL_TARGET_TD, B200RL_TARGET_TD)
+    CASE(B200RL_TARGET_UPGO, B200RL_TARGET_UPGO)
+    CASE(B200RL_TARGET_VTRACE, B200RL_TARGET_VTRACE)
+    CASE(B200RL_TARGET_TD, B200RL_TARGET_UPGO)
+    CASE(B200RL_TARGET_TD, B200RL_TARGET_VTRACE)
+    CASE(B200RL_TARGET_UPGO, B200RL_TARGET_TD)
+    CASE(B200RL_TARGET_UPGO, B200RL_TARGET_VTRACE)
+    CASE(B200RL_TARGET_VTRACE, B200RL_TARGET_TD)
+    CASE(B200RL_TARGET_VTRACE, B200RL_TARGET_UPGO)
+#undef CASE
+    return -1;
+}
+
+// Both heads in one launch; -1 when the pair is not eligible (the caller then launches the heads one by one).
+// A head without rewards has k.rew.p == nullptr.
+int b200rl_launch_target_rows2(int mt, int ma, const ScanParams& k0, const ScanParams& k1, cudaStream_t st) {
+    const int P = k0.P;
+    if (P != 1 && P != 2) return -1;
+    if (k0.B != k1.B || k0.T != k1.T || k1.P != P) return -1;
+    if ((k0.T % 4) != 0 || k0.T > B200RL_SHORT_T || k0.B < 1) return -1;
+    const bool need_rho = mt == B200RL_TARGET_VTRACE || ma == B200RL_TARGET_VTRACE;
+    bool rho_pp = false;
+    for (const ScanParams* k : {&k0, &k1}) {
+        if (!rows_ok(k->v, P, k->T)) return -1;
+        if (k->rew.p != nullptr && !rows_ok(k->rew, P, k->T)) return -1;
+        if (need_rho) {
+            if (k->rho.px != k->c.px) return -1;
+            const bool pp = P > 1 && k->rho.px == P;
+            if (k != &k0 && pp != rho_pp) return -1;
+            rho_pp = pp;
+            const int W = pp ? P : 1;
+            if (!rows_ok(k->rho, W, k->T) || !rows_ok(k->c, W, k->T)) return -1;
+            if (!pp && P > 1 && (k->rho.sp != 0 || k->c.sp != 0)) return -1;
+        }
+    }
+#define CASE(A, B_)                                                                                         \
+    if (mt == A && ma == B_) {                                                                              \
+        constexpr bool NR = (A == B200RL_TARGET_VTRACE || B_ == B200RL_TARGET_VTRACE);                      \
+        if (P == 1) return launch_dual<A, B_, 1, NR, false>(k0, k1, st);                                    \
+        if (NR && rho_pp) return launch_dual<A, B_, 2, NR, NR>(k0, k1, st);                                 \
+        return launch_dual<A, B_, 2, NR, false>(k0, k1, st);                                                \
+    }
     CASE(B200RL_TARGET_TD, B200RL_TARGET_TD)
     CASE(B200RL_TARGET_UPGO, B200RL_TARGET_UPGO)
     CASE(B200RL_TARGET_VTRACE, B200RL_TARGET_VTRACE)

@@ -266,21 +266,13 @@ int dispatch(int mt, int ma, ScanParams& k, bool has_rew, cudaStream_t st) {
 
 }  // namespace
 
-extern "C" int b200rl_target_scan_fused(int mode_targets, int mode_adv, const float* values, int64_t v_sb,
-                                        int64_t v_st, int64_t v_sp, const float* boot, int64_t boot_sb,
-                                        int64_t boot_sp, const float* rewards, int64_t r_sb, int64_t r_st,
-                                        int64_t r_sp, const float* rhos, int64_t rho_sb, int64_t rho_st,
-                                        int64_t rho_sp, const float* cs, int64_t c_sb, int64_t c_st, int64_t c_sp,
-                                        float* out_targets, float* out_adv, int64_t B, int64_t T, int64_t P,
-                                        double lmb, double gamma, void* stream) {
-    B200RL_REQUIRE(values && boot && out_targets && out_adv, "target_scan: null pointer");
-    B200RL_REQUIRE(((uintptr_t)out_targets % 16 == 0) && ((uintptr_t)out_adv % 16 == 0), "target_scan: outputs must be 16B aligned");
-    B200RL_REQUIRE(B >= 0 && T >= 1 && P >= 1 && P <= 128, "target_scan: bad shape B=%lld T=%lld P=%lld",
-                   (long long)B, (long long)T, (long long)P);
-    B200RL_REQUIRE(B < (1ll << 31) && T < (1ll << 31), "target_scan: shape too large");
-    const bool need_rho = mode_targets == B200RL_TARGET_VTRACE || mode_adv == B200RL_TARGET_VTRACE;
-    B200RL_REQUIRE(!need_rho || (rhos && cs), "target_scan: VTRACE needs rhos and cs");
-    if (B == 0) return B200RL_OK;
+namespace {
+
+ScanParams make_params(const float* values, int64_t v_sb, int64_t v_st, int64_t v_sp, const float* boot,
+                       int64_t boot_sb, int64_t boot_sp, const float* rewards, int64_t r_sb, int64_t r_st,
+                       int64_t r_sp, const float* rhos, int64_t rho_sb, int64_t rho_st, int64_t rho_sp,
+                       const float* cs, int64_t c_sb, int64_t c_st, int64_t c_sp, float* out_targets, float* out_adv,
+                       int64_t B, int64_t T, int64_t P, double lmb, double gamma) {
     ScanParams k;
     k.v = make_view(values, v_sb, v_st, v_sp, (int)P);
     k.v.px = (int)P;  // values always carry the player dim
@@ -305,11 +297,69 @@ extern "C" int b200rl_target_scan_fused(int mode_targets, int mode_adv, const fl
     k.lmb = (float)lmb;
     k.gamma = (float)gamma;
     k.gl = (float)(gamma * lmb);
+    return k;
+}
+
+int launch_one(int mode_targets, int mode_adv, ScanParams& k, cudaStream_t stream) {
     // contiguous P<=2 layouts (what compute_loss produces): row-per-thread cp.async pipeline
     static const bool force_generic = getenv("B200RL_TARGET_GENERIC") != nullptr;  // A/B switch for tools/sweep_targets.py
-    const int fast = force_generic ? -1 : b200rl_launch_target_rows(mode_targets, mode_adv, k, rewards != nullptr, (cudaStream_t)stream);
+    const bool has_rew = k.rew.p != nullptr;
+    const int fast = force_generic ? -1 : b200rl_launch_target_rows(mode_targets, mode_adv, k, has_rew, stream);
     if (fast >= 0) return fast;
-    return dispatch(mode_targets, mode_adv, k, rewards != nullptr, (cudaStream_t)stream);
+    return dispatch(mode_targets, mode_adv, k, has_rew, stream);
+}
+
+}  // namespace
+
+extern "C" int b200rl_target_scan_fused(int mode_targets, int mode_adv, const float* values, int64_t v_sb,
+                                        int64_t v_st, int64_t v_sp, const float* boot, int64_t boot_sb,
+                                        int64_t boot_sp, const float* rewards, int64_t r_sb, int64_t r_st,
+                                        int64_t r_sp, const float* rhos, int64_t rho_sb, int64_t rho_st,
+                                        int64_t rho_sp, const float* cs, int64_t c_sb, int64_t c_st, int64_t c_sp,
+                                        float* out_targets, float* out_adv, int64_t B, int64_t T, int64_t P,
+                                        double lmb, double gamma, void* stream) {
+    B200RL_REQUIRE(values && boot && out_targets && out_adv, "target_scan: null pointer");
+    B200RL_REQUIRE(((uintptr_t)out_targets % 16 == 0) && ((uintptr_t)out_adv % 16 == 0), "target_scan: outputs must be 16B aligned");
+    B200RL_REQUIRE(B >= 0 && T >= 1 && P >= 1 && P <= 128, "target_scan: bad shape B=%lld T=%lld P=%lld",
+                   (long long)B, (long long)T, (long long)P);
+    B200RL_REQUIRE(B < (1ll << 31) && T < (1ll << 31), "target_scan: shape too large");
+    const bool need_rho = mode_targets == B200RL_TARGET_VTRACE || mode_adv == B200RL_TARGET_VTRACE;
+    B200RL_REQUIRE(!need_rho || (rhos && cs), "target_scan: VTRACE needs rhos and cs");
+    if (B == 0) return B200RL_OK;
+    ScanParams k = make_params(values, v_sb, v_st, v_sp, boot, boot_sb, boot_sp, rewards, r_sb, r_st, r_sp, rhos, rho_sb,
+                               rho_st, rho_sp, cs, c_sb, c_st, c_sp, out_targets, out_adv, B, T, P, lmb, gamma);
+    return launch_one(mode_targets, mode_adv, k, (cudaStream_t)stream);
+}
+
+extern "C" int b200rl_target_scan_heads(int mode_targets, int mode_adv, const b200rl_target_head* heads, int n_heads,
+                                        int64_t B, int64_t T, int64_t P, double lmb, void* stream) {
+    B200RL_REQUIRE(heads && n_heads >= 1 && n_heads <= 2, "target_scan_heads: 1 or 2 heads");
+    B200RL_REQUIRE(B >= 0 && T >= 1 && P >= 1 && P <= 128, "target_scan_heads: bad shape B=%lld T=%lld P=%lld",
+                   (long long)B, (long long)T, (long long)P);
+    B200RL_REQUIRE(B < (1ll << 31) && T < (1ll << 31), "target_scan_heads: shape too large");
+    const bool need_rho = mode_targets == B200RL_TARGET_VTRACE || mode_adv == B200RL_TARGET_VTRACE;
+    ScanParams k[2];
+    for (int h = 0; h < n_heads; ++h) {
+        const b200rl_target_head& x = heads[h];
+        B200RL_REQUIRE(x.values && x.boot && x.out_targets && x.out_adv, "target_scan_heads: null pointer in head %d", h);
+        B200RL_REQUIRE(((uintptr_t)x.out_targets % 16 == 0) && ((uintptr_t)x.out_adv % 16 == 0),
+                       "target_scan_heads: outputs must be 16B aligned");
+        B200RL_REQUIRE(!need_rho || (x.rhos && x.cs), "target_scan_heads: VTRACE needs rhos and cs");
+        k[h] = make_params(x.values, x.v_sb, x.v_st, x.v_sp, x.boot, x.boot_sb, x.boot_sp, x.rewards, x.r_sb, x.r_st,
+                           x.r_sp, x.rhos, x.rho_sb, x.rho_st, x.rho_sp, x.cs, x.c_sb, x.c_st, x.c_sp, x.out_targets,
+                           x.out_adv, B, T, P, lmb, x.gamma);
+    }
+    if (B == 0) return B200RL_OK;
+    static const bool no_dual = getenv("B200RL_TARGET_GENERIC") != nullptr || getenv("B200RL_TARGET_NO_DUAL") != nullptr;
+    if (n_heads == 2 && !no_dual) {
+        const int rc = b200rl_launch_target_rows2(mode_targets, mode_adv, k[0], k[1], (cudaStream_t)stream);
+        if (rc >= 0) return rc;
+    }
+    for (int h = 0; h < n_heads; ++h) {
+        const int rc = launch_one(mode_targets, mode_adv, k[h], (cudaStream_t)stream);
+        if (rc != B200RL_OK) return rc;
+    }
+    return B200RL_OK;
 }
 
 extern "C" int b200rl_target_scan(int mode, const float* values, int64_t v_sb, int64_t v_st, int64_t v_sp,

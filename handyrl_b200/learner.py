@@ -1,8 +1,9 @@
 """Loss and data-parallel learner around the CUDA target recursion.
 
 * `forward_prediction`, `compose_losses`, `compute_loss` keep the signatures and semantics of
-  handyrl/train.py:136-258; the four `compute_target` calls of train.py:248-253 collapse into one fused
-  `compute_target_pair` per head (targets of `value_target`, advantages of `policy_target`).
+  handyrl/train.py:136-258; the four `compute_target` calls of train.py:248-253 collapse into one
+  `compute_target_heads` call (per head: targets of `value_target`, advantages of `policy_target`; both heads in
+  one kernel launch for rows of <= 64 steps).
 * `DataParallelLearner` replaces `nn.DataParallel` (train.py:365-366) and the pickled weight hand-off to the
   workers (train.py:613, worker.py:52) with one process per GPU: gradients are averaged with ONE all-reduce over
   a flat fp32 bucket, parameters + buffers are broadcast from rank 0 as one flat tensor.
@@ -13,7 +14,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 
 from . import _lib
-from .losses import compute_target_pair
+from .losses import compute_target_heads
 
 
 def _map(x, fn):
@@ -160,12 +161,12 @@ def compute_loss(batch, model, hidden, args, fused=True):
                 v = (v - v.flip(2)) / (batch['observation_mask'].sum(dim=2, keepdim=True) + 1e-8)
             nograd['value'] = v * emask + batch['outcome'] * (1 - emask)
     targets, advantages = {}, {}
-    targets['value'], advantages['value'] = compute_target_pair(
-        args['value_target'], args['policy_target'], nograd.get('value'), batch['outcome'], None,
-        args['lambda'], 1, clipped_rhos, cs)
-    targets['return'], advantages['return'] = compute_target_pair(
-        args['value_target'], args['policy_target'], nograd.get('return'), batch['return'], batch['reward'],
-        args['lambda'], args['gamma'], clipped_rhos, cs)
+    # train.py:248-253: value head (bootstrap = outcome, no rewards, gamma 1) and return head, one kernel launch
+    (targets['value'], advantages['value']), (targets['return'], advantages['return']) = compute_target_heads(
+        args['value_target'], args['policy_target'],
+        [(nograd.get('value'), batch['outcome'], None, 1),
+         (nograd.get('return'), batch['return'], batch['reward'], args['gamma'])],
+        args['lambda'], clipped_rhos, cs)
     total_advantages = clipped_rhos * sum(advantages.values())
     return compose_losses(outputs, logp_t, total_advantages, targets, batch, args)
 
@@ -240,4 +241,4 @@ class DataParallelLearner:
         self.data_cnt_ema = self.data_cnt_ema * 0.8 + dcnt * 0.2   # reference: updated per epoch from the batch counts
         for g in self.optimizer.param_groups:
             g['lr'] = self.default_lr * self.data_cnt_ema / (1 + self.steps * 1e-5)
-        return {k: float(v) for k, v in losses.items()}, dcnt
+        return {k: float(v.detach()) for k, v in losses.items()}, dcnt

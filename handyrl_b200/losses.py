@@ -265,3 +265,66 @@ def compute_target_pair(value_target, policy_target, values, returns, rewards, l
         _, a = compute_target(policy_target, values, returns, rewards, lmb, gamma, rhos, cs)
         return t, a
     return _scan(MODES[value_target], MODES[policy_target], values, returns, rewards, lmb, gamma, rhos, cs)
+
+
+def compute_target_heads(value_target, policy_target, heads, lmb, rhos, cs):
+    """Additive API: `compute_target_pair` for all heads of one loss in one call.
+
+    `heads` is a list of `(values, returns, rewards, gamma)` — what handyrl/train.py:248-253 passes for the value
+    head `(values, outcome, None, 1)` and the return head `(returns_pred, returns, rewards, gamma)`; a head whose
+    `values` is None yields `(None, 0)` like `compute_target`.  With two live heads of the same 4-D shape both
+    recursions run in one kernel launch (`b200rl_target_scan_heads`); every other case falls back to one
+    `compute_target_pair` per head.  Results are bit-identical to the per-head calls."""
+    live = [h for h in heads if h[0] is not None]
+    fused = None
+    if (len(live) == 2 and value_target in MODES and policy_target in MODES
+            and 'MC' not in (value_target, policy_target)):
+        fused = _scan_heads_4d(MODES[value_target], MODES[policy_target], live, lmb, rhos, cs)
+    out = []
+    for h in heads:
+        if h[0] is None:
+            out.append((None, 0))
+        elif fused is not None:
+            out.append(fused.pop(0))
+        else:
+            out.append(compute_target_pair(value_target, policy_target, h[0], h[1], h[2], lmb, h[3], rhos, cs))
+    return out
+
+
+def _scan_heads_4d(mode_t, mode_a, heads, lmb, rhos, cs):
+    """Both heads through b200rl_target_scan_heads; None when the inputs are not the 4-D compute_loss shapes."""
+    vs = heads[0][0].shape
+    if len(vs) != 4 or vs[3] != 1:
+        return None
+    B, T, P = vs[0], vs[1], vs[2]
+    if B == 0 or (B * T * P) % 4 != 0:
+        return None
+    need_rho = mode_t == 3 or mode_a == 3
+    if need_rho and not (rhos is not None and cs is not None and _is4(rhos, B, T, P) and _is4(cs, B, T, P)):
+        return None
+    dev = heads[0][0].device
+    arr = (_lib.TargetHead * 2)()
+    out = torch.empty((2, 2, B, T, P, 1), dtype=torch.float32, device=dev)
+    rho = _v4(rhos, B, T, P) if need_rho else (0, 0, 0, 0)
+    c = _v4(cs, B, T, P) if need_rho else (0, 0, 0, 0)
+    for i, (values, returns, rewards, gamma) in enumerate(heads):
+        if (tuple(values.shape) != tuple(vs) or values.dtype != torch.float32 or not values.is_cuda
+                or values.device != dev or returns.dim() != 4 or not _is4(returns, B, returns.shape[1], P)):
+            return None
+        if rewards is not None and not _is4(rewards, B, T, P):
+            return None
+        rs, rst = returns.shape, returns.stride()
+        h = arr[i]
+        h.values, h.v_sb, h.v_st, h.v_sp = _v4(values, B, T, P)
+        h.boot = returns.data_ptr() + 4 * rst[1] * (rs[1] - 1)          # returns[:, -1]
+        h.boot_sb = rst[0] if (rs[0] == B and B > 1) else 0
+        h.boot_sp = rst[2] if (rs[2] == P and P > 1) else 0
+        h.rewards, h.r_sb, h.r_st, h.r_sp = _v4(rewards, B, T, P) if rewards is not None else (None, 0, 0, 0)
+        h.rhos, h.rho_sb, h.rho_st, h.rho_sp = rho if need_rho else (None, 0, 0, 0)
+        h.cs, h.c_sb, h.c_st, h.c_sp = c if need_rho else (None, 0, 0, 0)
+        h.out_targets, h.out_adv = out[i, 0].data_ptr(), out[i, 1].data_ptr()
+        h.gamma = float(gamma)
+    rc = _call_on(dev, _lib.lib().b200rl_target_scan_heads, mode_t, mode_a, ctypes.addressof(arr), 2, B, T, P,
+                  float(lmb))
+    _lib.check(rc, "b200rl_target_scan_heads")
+    return [(out[0, 0], out[0, 1]), (out[1, 0], out[1, 1])]

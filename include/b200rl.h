@@ -64,6 +64,28 @@ int b200rl_target_scan_fused(int mode_targets, int mode_adv, const float* values
                              double lmb, double gamma, void* stream);
 
 /*
+ * The heads of one loss in one call.  handyrl/train.py:248-253 runs the target recursion once for the value
+ * head (bootstrap = outcome, rewards None, gamma 1) and once for the return head (rewards, gamma) with the same
+ * modes, lambda, shape and rhos/cs; for rows of <= 64 steps both heads run in ONE kernel launch (a head is a
+ * 13-16 us kernel at B = 65,536, T = 32: two launches pay ramp-up and drain twice).  Per-head fields have the
+ * meaning of the b200rl_target_scan arguments of the same name; rewards == NULL is `rewards is None`.
+ * n_heads is 1 or 2.  Results are bit-identical to n_heads calls of b200rl_target_scan_fused.
+ */
+typedef struct b200rl_target_head {
+    const float* values; int64_t v_sb, v_st, v_sp;
+    const float* boot; int64_t boot_sb, boot_sp;
+    const float* rewards; int64_t r_sb, r_st, r_sp;
+    const float* rhos; int64_t rho_sb, rho_st, rho_sp;
+    const float* cs; int64_t c_sb, c_st, c_sp;
+    float* out_targets;
+    float* out_adv;
+    double gamma;
+} b200rl_target_head;
+
+int b200rl_target_scan_heads(int mode_targets, int mode_adv, const b200rl_target_head* heads, int n_heads,
+                             int64_t B, int64_t T, int64_t P, double lmb, void* stream);
+
+/*
  * monte_carlo (handyrl/losses.py:16-17): out_adv = returns - values with
  * broadcasting; the target is `returns` itself (aliased by the Python shim).
  */

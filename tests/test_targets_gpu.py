@@ -122,6 +122,34 @@ def test_long_rows_ws_kernel(monkeypatch, B, T, P, rpp, vt, pt, head):
         _close(a1, np.asarray(ra2))
 
 
+@pytest.mark.parametrize("B,T,P,rpp", [(4096, 32, 2, False), (777, 16, 2, True), (333, 64, 1, False), (100, 200, 2, False),
+                                       (65, 33, 4, False), (50, 7, 2, False)])
+@pytest.mark.parametrize("vt,pt", [('VTRACE', 'UPGO'), ('UPGO', 'VTRACE'), ('TD', 'TD'), ('MC', 'UPGO')])
+def test_heads_equal_per_head_calls(B, T, P, rpp, vt, pt):
+    """compute_target_heads (value head: outcome bootstrap, rewards None, gamma 1; return head: rewards, gamma
+    0.8) runs both heads in one launch for short contiguous rows and falls back to one call per head otherwise;
+    either way the bits are those of compute_target_pair per head, and of the oracle."""
+    from handyrl_b200.losses import compute_target_heads, compute_target_pair
+    dv = target_inputs(B, T, P, 'value', rpp, seed=B + T)
+    dr = target_inputs(B, T, P, 'return', rpp, seed=B + T + 1)
+    gv, gr = _cuda(dv), _cuda(dr)
+    rho, c = gr['rhos'], gr['cs']
+    heads = [(gv['values'], gv['returns'], None, 1), (gr['values'], gr['returns'], gr['rewards'], 0.8)]
+    for cs_t in (c, rho):     # two tensors / one aliased tensor
+        res = compute_target_heads(vt, pt, heads, 0.7, rho, cs_t)
+        for (tg, adv), h in zip(res, heads):
+            t1, a1 = compute_target_pair(vt, pt, h[0], h[1], h[2], 0.7, h[3], rho, cs_t)
+            assert torch.equal(tg, t1) and torch.equal(adv, a1)
+    (tg, adv), _ = compute_target_heads(vt, pt, heads, 0.7, rho, c)
+    rt, _ = targets_np.compute_target(vt, dv['values'], dv['returns'], None, 0.7, 1, dr['rhos'], dr['cs'])
+    _, ra = targets_np.compute_target(pt, dv['values'], dv['returns'], None, 0.7, 1, dr['rhos'], dr['cs'])
+    _close(tg, np.asarray(rt))
+    _close(adv, np.asarray(ra))
+    # a missing head behaves like compute_target(None, ...)
+    res = compute_target_heads(vt, pt, [(None, None, None, 1), heads[1]], 0.7, rho, c)
+    assert res[0] == (None, 0) and torch.equal(res[1][0], compute_target_pair(vt, pt, *heads[1][:3], 0.7, 0.8, rho, c)[0])
+
+
 def test_noncontiguous_and_broadcast_views():
     from handyrl_b200.losses import compute_target
     d = target_inputs(50, 20, 2, 'return', seed=9)
