@@ -1,17 +1,20 @@
-// Row-per-thread target recursion with a cp.async shared-memory pipeline (sm_100a).
+// Target recursion for the layouts compute_loss actually produces (sm_100a): shared-memory pipelines fed by cp.async.
 //
-// Fast path of b200rl_target_scan for the layouts compute_loss actually produces
-// (handyrl/train.py:218-258): P in {1,2}, values / rewards contiguous (B,T,P), rhos / cs either
-// (B,T,1) broadcast over players (turn-based training) or (B,T,P), T % 4 == 0, 16-byte aligned.
+// Fast paths of b200rl_target_scan / _fused / _heads (handyrl/train.py:218-258): P in {1,2}, values / rewards
+// contiguous (B,T,P), rhos / cs either (B,T,1) broadcast over players (turn-based training) or (B,T,P),
+// T % 4 == 0, 16-byte aligned.  Everything else goes to the generic kernel in target_scan.cu.
 //
-// One WARP owns a tile of TR batch rows and walks it backward in chunks of RTC timesteps (shapes below).
-// Chunks are fetched with 16-byte cp.async (coalesced along the rows, no register staging) into a
-// warp-private ring of NS stages, so the loads of chunk k-1 .. k-NS+1 are in flight while chunk k
-// is scanned.  Each lane scans ONE row — P independent sequences, which gives the dependent fp32
-// chains some ILP — reading its row with conflict-free LDS.128 (row stride = TC*P+4 floats, i.e. an
-// odd number of 16-byte units) and writing targets / advantages in place; the warp then streams the
-// tile out with coalesced 128-bit stores.  No __syncthreads, no CTA-wide phases: warps drift freely,
-// and a persistent grid-stride over tiles keeps the 148 SMs evenly loaded.
+// Rows of <= 64 steps (k_target_rows, k_target_rows2): one WARP (= one CTA, so the hardware hands tiles to SMs as
+// they free up) owns a tile of 32 batch rows and walks it backward in chunks of 16 timesteps.  Chunks are fetched
+// with 16-byte cp.async (coalesced along the rows, no register staging) into a warp-private ring of 2-4 stages, so
+// the loads of the next chunks are in flight while one is scanned.  Each lane scans ONE row — P independent
+// sequences, which gives the dependent fp32 chains some ILP — reading its row with conflict-free LDS.128 (row
+// stride = RTC*P+4 floats, an odd number of 16-byte units) and writing targets / advantages in place; the warp
+// then streams the tile out with coalesced 128-bit stores.  No __syncthreads, no CTA-wide phases.
+// k_target_rows2 runs the value head and the return head of one loss in one launch.
+//
+// Longer rows (k_target_rows_ws): three specialised warps per tile — loader, compute (one sequence per lane),
+// storer — around an mbarrier ring; see the comment at the kernel.
 //
 // Arithmetic is the same Rec<> code as the generic kernel: bit-identical to torch fp32.
 #include <cstdlib>
@@ -27,10 +30,10 @@ namespace {
 #ifndef B200RL_NSTAGE
 #define B200RL_NSTAGE 2
 #endif
-// Tile shapes (TR batch rows per warp x RTC timesteps per chunk).  What HBM delivers for this access pattern is set
-// by the contiguous bytes fetched per row (tools/probe_rows.cu: 128 B -> 4.9 TB/s, 256 B -> 5.8 TB/s, 1 KB -> 6.0 of a
-// 6.2 TB/s streaming copy), so long rows use 16 rows x 32 steps (256 B per row at P = 2; lanes >= 16 only help
-// with the copies) and short rows, where a whole 32-row tile is one contiguous block anyway, keep 32 x 16.
+// Tile shapes (batch rows per tile x timesteps per chunk).  What HBM delivers for this access pattern is set by the
+// contiguous bytes fetched per row (tools/probe_rows.cu: 128 B -> 4.9 TB/s, 256 B -> 5.8 TB/s, 1 KB -> 6.0 of a
+// 6.2 TB/s streaming copy), so long rows fetch 256-512 B per row and chunk (16 rows x 32-64 steps at P = 2) and
+// short rows, where a whole 32-row tile is one contiguous block anyway, use 32 x 16.
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
@@ -574,6 +577,25 @@ __global__ void __launch_bounds__(96) k_target_rows_ws(const ScanParams k, int c
 
 namespace {
 
+// One-time setup per DEVICE and kernel instantiation (the opt-in shared-memory attribute is per device, and a process
+// may drive more than one); returns the SM count of the current device.  Races are benign: the setup is idempotent.
+struct DevOnce {
+    unsigned long long done = 0;
+    int sms[64] = {};
+};
+template <class F>
+int dev_setup(DevOnce& o, F&& set_attr) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 63;
+    if (!((o.done >> dev) & 1ull)) {
+        cudaDeviceGetAttribute(&o.sms[dev], cudaDevAttrMultiProcessorCount, dev);
+        set_attr();
+        o.done |= 1ull << dev;
+    }
+    return o.sms[dev];
+}
+
 constexpr int NSTAGE = B200RL_NSTAGE;  // ring depth when the grid fills the machine
 
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int TR, int RTC>
@@ -583,15 +605,12 @@ int launch_shape(const ScanParams& k, cudaStream_t st) {
     const bool alias = NEED_RHO && k.c.p == k.rho.p && k.c.sb == k.rho.sb && k.c.st == k.rho.st && k.c.sp == k.rho.sp;
     const int stage = TR * (2 * RSV + (NEED_RHO ? (alias ? RSR : 2 * RSR) : 0));
     auto kern = k_target_rows<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, TR, RTC>;
-    static int sms = 0;
     static int per_sm_tab[2][3] = {};  // resident warps per SM of this instantiation by [c aliases rho][ns - 2]
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    static DevOnce once;
+    const int sms = dev_setup(once, [&] {
         constexpr size_t SMEM_MAX = (size_t)4 * TR * (2 * RSV + 2 * RSR) * sizeof(float);
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
-    }
+    });
     const int ntiles = (k.B + TR - 1) / TR;
     // deepen the ring while all tiles still fit on the SMs at once (small B: latency-bound per warp)
     const int want = (ntiles + sms - 1) / sms;
@@ -627,14 +646,11 @@ int launch_dual(const ScanParams& k0, const ScanParams& k1, cudaStream_t st) {
     if (alias != is_alias(k1)) return -1;
     const int stage = TR * (2 * RSV + (NEED_RHO ? (alias ? RSR : 2 * RSR) : 0));
     auto kern = k_target_rows2<MT, MA, P, NEED_RHO, RHO_PP, TR, RTC>;
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    static DevOnce once;
+    const int sms = dev_setup(once, [&] {
         constexpr size_t SMEM_MAX = (size_t)4 * TR * (2 * RSV + 2 * RSR) * sizeof(float);
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
-    }
+    });
     const int ntiles = (k0.B + TR - 1) / TR;
     const int want = (2 * ntiles + sms - 1) / sms;
     int ns = NSTAGE;
@@ -657,15 +673,12 @@ int launch_ws(const ScanParams& k, cudaStream_t st) {
     const size_t stage = sizeof(float) * TR * (2 * RSV + (NEED_RHO ? (alias ? RSR : 2 * RSR) : 0));
     auto kern = k_target_rows_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, RTC>;
     constexpr size_t BAR = WS_BAR_FLOATS * sizeof(float);
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    static DevOnce once;
+    const int sms = dev_setup(once, [&] {
         constexpr size_t SMEM_ALL = BAR + (size_t)WS_MAX_STAGES * sizeof(float) * TR * (2 * RSV + 2 * RSR);
         constexpr size_t SMEM_MAX = SMEM_ALL < WS_SMEM_CAP ? SMEM_ALL : WS_SMEM_CAP;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX);
-    }
+    });
     const int ntiles = (k.B + TR - 1) / TR;
     const int want = (ntiles + sms - 1) / sms;   // CTAs an SM holds when the whole grid is resident
     const char* ns_e = getenv("B200RL_TARGET_WS_STAGES");
