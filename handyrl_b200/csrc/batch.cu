@@ -5,6 +5,7 @@
 // state, the action(s) and episode flags.  make_batch re-encodes observation,
 // policy and action_mask from the record instead of copying 2.8 kB of fp32 per
 // (b, t): HBM reads are 32 B per cell, writes are the batch tensors themselves.
+#include <atomic>
 #include <condition_variable>
 #include <functional>
 #include <mutex>
@@ -573,8 +574,9 @@ public:
         cv_work_.notify_all();
         for (auto& t : th_) t.join();
     }
-    // runs f(0..n-1) on n pool threads and returns when all are done; one caller at a time
-    void run(int n, const std::function<void(int)>& f) {
+    // runs f(0..n-1) on n pool threads and `mine` on the calling thread, returns when all are done; one caller at
+    // a time
+    void run(int n, const std::function<void(int)>& f, const std::function<void()>& mine) {
         std::lock_guard<std::mutex> serial(run_mu_);
         std::unique_lock<std::mutex> lk(m_);
         while ((int)th_.size() < n) {
@@ -586,6 +588,9 @@ public:
         pending_ = n;
         ++generation_;
         cv_work_.notify_all();
+        lk.unlock();
+        mine();
+        lk.lock();
         cv_done_.wait(lk, [this] { return pending_ == 0; });
         job_ = nullptr;
     }
@@ -656,11 +661,18 @@ extern "C" int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t 
         work(0, B);
         return B200RL_OK;
     }
-    const int64_t per = (B + n_threads - 1) / n_threads;
-    host_pool().run(n_threads, [&](int t) {
-        const int64_t lo = t * per, hi = lo + per < B ? lo + per : B;
-        if (lo < hi) work(lo, hi);
-    });
+    // Blocks of 1024 windows handed out from a shared counter (a thread that loses its core for a while — eight
+    // ranks share the box's cores — no longer holds up the call), and the calling thread works too.
+    constexpr int64_t BLOCK = 1024;
+    std::atomic<int64_t> next{0};
+    auto drain = [&] {
+        for (;;) {
+            const int64_t lo = next.fetch_add(BLOCK, std::memory_order_relaxed);
+            if (lo >= B) break;
+            work(lo, lo + BLOCK < B ? lo + BLOCK : B);
+        }
+    };
+    host_pool().run(n_threads - 1, [&](int) { drain(); }, drain);
     return B200RL_OK;
 }
 
