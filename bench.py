@@ -315,8 +315,8 @@ def main():
     e2e = None
     if not args.no_e2e:
         # Software-pipelined like the reference's asynchronous batchers: while the GPU runs rollout k and the
-        # batch/targets of the windows chosen from rollouts <= k-1, the host reads back the finished-episode rows
-        # of rollout k and draws the next windows.
+        # batch/targets of the windows chosen from rollouts <= k-2, the host draws the next windows from the rows of
+        # rollouts <= k-1 and then takes in the finished-episode rows of rollout k.
         st = gen.store
         torch.cuda.synchronize()
         index = HostReplayIndex(gen, max_new_rows=1 << 15, n_threads=max(1, min(8, (os.cpu_count() or 1) // world)))
@@ -369,19 +369,20 @@ def main():
                 ev_done.record()
                 hs["pending"] = True
             t_d = pc()
-            # ---- host work, overlapped with the GPU: index the new episodes, draw the next windows ----
-            index.commit()
-            t_e = pc()
-            hs["d2h"] = index.d2h_bytes
+            # ---- host work, overlapped with the GPU: draw the next windows from the episodes indexed so far (the
+            # rows of rollouts <= k-1), THEN take in the rows of rollout k, whose read-back has landed by then ----
             slot = hs["slot"]
             hs["slot"] ^= 1
-            buf = index.select(B, TRAIN_ARGS, win_pin[slot], seed=rank)
+            buf = index.select(B, TRAIN_ARGS, win_pin[slot], seed=rank, lookahead=PLIES)
             with torch.cuda.stream(copy_stream):                                # H2D: windows for the next step
                 win_devs[slot].copy_(buf, non_blocking=True)
                 ev_h2d[slot].record()
             hs["win"], hs["h2d"] = win_devs[slot], ev_h2d[slot]
+            t_e = pc()
+            index.commit()
+            hs["d2h"] = index.d2h_bytes
             t_f = pc()
-            for name, dt_ in zip(tr_acc, (t_b - t_a, t_c - t_b, t_d - t_c, t_e - t_d, t_f - t_e)):
+            for name, dt_ in zip(tr_acc, (t_b - t_a, t_c - t_b, t_d - t_c, t_f - t_e, t_e - t_d)):
                 tr_acc[name] += dt_
 
         for k in range(4):

@@ -62,7 +62,9 @@ class HostReplayIndex:
     device-resident trajectory store: a pinned mirror of the finished-episode table.  Only these 16-byte rows
     cross PCIe; the moments stay in the trajectory ring.  `fetch_async` enqueues the read-back behind the
     rollout on the current stream, `commit` waits for it, `select` draws windows with the SAME rule and RNG as
-    the device kernel (`b200rl_select_windows_host`) into a pinned buffer ready for upload."""
+    the device kernel (`b200rl_select_windows_host`) into a pinned buffer ready for upload.  `select` may run while
+    a `fetch_async` is in flight (it only reads rows below the committed cursor) as long as
+    `maximum_episodes + max_new_rows <= E`, i.e. the incoming rows do not wrap onto the ones being drawn from."""
 
     def __init__(self, gen, max_new_rows=1 << 15, n_threads=4):
         st = gen.store
@@ -99,12 +101,15 @@ class HostReplayIndex:
         self.read = self.cursor = cur
         return cur
 
-    def select(self, batch_size, args, out_pinned, seed=0):
+    def select(self, batch_size, args, out_pinned, seed=0, lookahead=0):
+        """`lookahead` = plies that will be generated between this call and the use of the windows (a pipelined
+        caller draws the windows of the next step while the current rollout runs): episodes whose first plies the
+        ring will have overwritten by then are skipped like rejected draws."""
         if self.cursor <= 0:
             raise _lib.B200RLError("HostReplayIndex.select: no finished episodes indexed yet")
         a = int(args['maximum_episodes'])
         _lib.call("b200rl_select_windows_host", ctypes.c_void_p(self.table.data_ptr()), self.st.E, self.cursor, a,
-                  int(args['forward_steps']), int(seed) ^ 0x5E1EC7, self.draws, self.st.it, self.st.D,
+                  int(args['forward_steps']), int(seed) ^ 0x5E1EC7, self.draws, self.st.it + int(lookahead), self.st.D,
                   ctypes.c_void_p(out_pinned.data_ptr()), int(batch_size), self.n_threads)
         self.draws += 256
         return out_pinned
