@@ -157,3 +157,28 @@ def test_host_replay_index_equals_device_selection():
     gen._draws = 0
     dev = gen.select_windows(256, a, seed=7).cpu()
     assert torch.equal(host, dev)
+
+
+@pytest.mark.gpu
+def test_lookahead_keeps_windows_inside_the_ring():
+    """A pipelined caller draws windows, generates `lookahead` more plies, then builds the batch: with
+    select(lookahead=K) every chosen episode still has its first ply in the trajectory ring after those K plies
+    (without it, episodes that began within K plies of the ring's far edge could be chosen)."""
+    import torch
+    from handyrl_b200.generation import BatchGenerator, HostReplayIndex
+    D, K = 256, 64
+    gen = BatchGenerator('TicTacToe', 2048, seed=3, depth=D, max_episodes=1 << 16)
+    gen.rollout(D + 40)                                   # the ring has wrapped: old episodes are gone
+    idx = HostReplayIndex(gen, n_threads=2)
+    a = dict(ARGS, maximum_episodes=60000, forward_steps=4)   # ~220 plies of finished episodes: some near the edge
+    pin = torch.empty(4096, 8, dtype=torch.int32).pin_memory()
+    w = idx.select(4096, a, pin, seed=1, lookahead=K).clone()
+    it_use = gen.store.it + K                             # iteration counter when the batch would be built
+    first = w[:, 1].to(torch.int64) & 0xFFFFFFFF | (w[:, 2].to(torch.int64) << 32)
+    start_of_episode = first - w[:, 4].to(torch.int64)    # window start minus its offset in the episode
+    assert bool((it_use - start_of_episode <= D).all())
+    w0 = idx.select(4096, a, pin, seed=1, lookahead=0)
+    first0 = w0[:, 1].to(torch.int64) & 0xFFFFFFFF | (w0[:, 2].to(torch.int64) << 32)
+    assert bool((gen.store.it - (first0 - w0[:, 4].to(torch.int64)) <= D).all())
+    # the case is not vacuous: without the lookahead some of the chosen episodes would be overwritten by then
+    assert not bool((it_use - (first0 - w0[:, 4].to(torch.int64)) <= D).all())
