@@ -327,6 +327,16 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
     __shared__ int4 ep_buf[WARPS][EP_BUF];
     int ep_n = 0;            // rows waiting in ep_buf[warp] (warp-uniform)
 
+    int64_t pend_grp = -1;       // group whose progress word still has to be published (warp-uniform)
+    unsigned int pend_val = 0;
+    auto publish = [&]() {
+        if (pend_grp >= 0) {
+            __threadfence();     // every lane: its state stores before the flag
+            __syncwarp();
+            if (lane == 0) st_release_u32(p.sched + SCHED_HDR + pend_grp, pend_val);
+            pend_grp = -1;
+        }
+    };
     for (;;) {
         unsigned int tk = 0;
         if (lane == 0) tk = atomicAdd(&p.sched[0], 1u);
@@ -338,19 +348,30 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
         const bool valid = lane < ng;
         const int64_t i = g0 + lane;
         if (ch > 0) {   // the previous chunk of this group must have stored its states
-            if (lane == 0) {
-                unsigned int spins = 0;
-                while (ld_acquire_u32(p.sched + SCHED_HDR + grp) < (unsigned int)ch) {
-                    __nanosleep(100);
-                    if (++spins > (1u << 24)) break;   // ~2 s: never hang the GPU on a scheduling bug
+            const unsigned int* flag = p.sched + SCHED_HDR + grp;
+            bool ready = true;
+            if (lane == 0) ready = ld_acquire_u32(flag) >= (unsigned int)ch;
+            ready = __shfl_sync(0xffffffffu, ready ? 1 : 0, 0) != 0;
+            if (!ready) {
+                publish();   // never wait while holding back a publication of our own (it may be what others need)
+                if (lane == 0) {
+                    unsigned int spins = 0;
+                    while (ld_acquire_u32(flag) < (unsigned int)ch) {
+                        __nanosleep(100);
+                        if (++spins > (1u << 24)) break;   // ~2 s: never hang the GPU on a scheduling bug
+                    }
                 }
+                __syncwarp();
             }
-            __syncwarp();
-            __threadfence();
+            (void)ld_acquire_u32(flag);   // every lane acquires for itself (a fence here would also wait for OUR stores)
         }
         typename G::State s;
         G::reset(s);
         if (valid) s = G::load_cg(p.state, p.N, i);
+        // Publication of the PREVIOUS ticket, deferred to here: its fence has to wait until that ticket's ~256 KB of
+        // streaming stores are performed; issued right after them it was 13 % of the kernel's stall samples, issued
+        // behind the ticket take and this state load most of that drain has already happened.
+        publish();
         const uint64_t stream_id = p.game_id_base + (uint64_t)i;
         const int64_t k_begin = ch * p.chunk, k_end = min(k_begin + p.chunk, p.n_plies);
 
@@ -460,12 +481,12 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
         }
         if (valid) G::store(p.state, p.N, i, s);
         n_steps += (unsigned long long)ng * (unsigned long long)(k_end - k_begin);
-        if (nchunks > 1) {   // publish: states of this group are valid up to chunk ch
-            __threadfence();
-            __syncwarp();
-            if (lane == 0) st_release_u32(p.sched + SCHED_HDR + grp, (unsigned int)(ch + 1));
+        if (nchunks > 1) {   // to publish: states of this group are valid up to chunk ch
+            pend_grp = grp;
+            pend_val = (unsigned int)(ch + 1);
         }
     }
+    publish();
     if (p.counters) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
