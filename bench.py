@@ -177,12 +177,17 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     hp, cores = cpu_hotpath_runner(0)
+    # one reference step = the N=1 workload of one step (N_GAMES games x PLIES plies), as `inner` rounds of
+    # cores x 256 games: ~0.3 s per step on 16 cores, so that K = 20 steps are a 6 s sample and not 0.4 s
+    inner = max(1, N_GAMES // (cores * CPU_GAMES_PER_THREAD))
     for _ in range(args.warmup):
-        hp.step()
+        for _ in range(inner):
+            hp.step()
     t0 = time.perf_counter()
     total = 0
     for k in range(args.steps):
-        total += hp.step()[0]
+        for _ in range(inner):
+            total += hp.step()[0]
     dt = time.perf_counter() - t0
     v = total / dt
     line = {
@@ -191,7 +196,7 @@ def run_reference(args, rank, world):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32 cell arrays -> f32",
         "data": "synthetic", "config": workload_config(args.gpus),
         "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                         "sample": cpu_sample_text(cores, args.steps, dt)},
+                         "sample": cpu_sample_text(cores, args.steps * inner, dt)},
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
