@@ -3,11 +3,24 @@
 Rules, legal moves and observation encoding always run in the CUDA kernels; the host side
 only keeps what the reference keeps in Python lists/dicts for its string protocol
 (`record`, `layouts`) and reads back small results.
+
+Process model.  The reference builds the environment in the parent (`Learner.__init__`,
+handyrl/train.py:428; `eval_main`, handyrl/evaluation.py:294) and then *forks* its workers, each of
+which builds the environment again (handyrl/worker.py:32,189; handyrl/evaluation.py:151,210).  A CUDA
+context does not survive `fork`, so the facade never touches the device in `__init__`, `players()`,
+`action_length()` or `net()`: the 1-slot `BatchedEnv` is created on the first call that needs the game
+state, in the process that makes that call.  A facade object inherited through `fork` drops the parent's
+engine handle and starts from a fresh game in the child (what the reference's workers do anyway: they
+`reset()` before every episode).
 """
+import ctypes
+import os
+
 import numpy as np
 import torch
 
-from ..engine import BatchedEnv, VIEW_NONE
+from .. import _lib
+from ..engine import GAMES, BatchedEnv, VIEW_NONE
 from ..environment import BaseEnvironment
 
 
@@ -15,17 +28,49 @@ def _default_device():
     return torch.device("cuda", torch.cuda.current_device())
 
 
+def _static_dims(game):
+    """(A, ...) of a game from the library's host-side table: no CUDA call."""
+    dims = (ctypes.c_int64 * 8)()
+    _lib.call("b200rl_env_dims", GAMES[game], ctypes.cast(dims, ctypes.c_void_p))
+    return [int(x) for x in dims]
+
+
 class DeviceEnvironment(BaseEnvironment):
     GAME = None
 
     def __init__(self, args=None):
         super().__init__()
-        dev = (args or {}).get('device') if isinstance(args, dict) else None
-        self._env = BatchedEnv(self.GAME, 1, device=dev or _default_device())
+        self._device_arg = (args or {}).get('device') if isinstance(args, dict) else None
+        self._engine = None
+        self._engine_pid = None
         self._info = None
-        self.reset()
+        self._A = _static_dims(self.GAME)[0]
+        self._host_reset({})
 
     # -- engine access -----------------------------------------------------
+    @property
+    def _env(self):
+        """The 1-slot engine of THIS process, created on first use (never in __init__)."""
+        pid = os.getpid()
+        if self._engine is None or self._engine_pid != pid:
+            if self._engine is not None:
+                # inherited through fork: the parent's context is unusable here
+                self._engine = None
+                self._host_reset({})
+            if torch.cuda._is_in_bad_fork():
+                raise _lib.B200RLError(
+                    "the parent process initialised CUDA before forking this process; a forked child cannot "
+                    "create a CUDA context.  Construct the environment before the first CUDA call of the parent "
+                    "(the facades defer theirs) or use the 'spawn' start method")
+            self._engine = BatchedEnv(self.GAME, 1, device=self._device_arg or _default_device())
+            self._engine_pid = pid
+            self._info = None
+        return self._engine
+
+    def _host_reset(self, args):
+        """Host-side part of reset(): the fields of the reference's string protocol."""
+        self.record = []
+
     def _dirty(self):
         self._info = None
 
@@ -40,15 +85,22 @@ class DeviceEnvironment(BaseEnvironment):
 
     def _raw_state(self):
         """uint32 words of the slot's state (layout in DESIGN.md)"""
-        w = self._env.state_bytes // 4
-        return self._env.state[:w].cpu().numpy().view(np.uint32).copy()
+        env = self._env
+        w = env.state_bytes // 4
+        return env.state[:w].cpu().numpy().view(np.uint32).copy()
 
     def _set_raw_state(self, words):
-        w = self._env.state_bytes // 4
-        self._env.state[:w].copy_(torch.from_numpy(np.asarray(words, dtype=np.uint32).view(np.int32)))
+        env = self._env
+        w = env.state_bytes // 4
+        env.state[:w].copy_(torch.from_numpy(np.asarray(words, dtype=np.uint32).view(np.int32)))
         self._dirty()
 
     # -- reference interface -------------------------------------------------
+    def reset(self, args={}):
+        self._env.reset()
+        self._dirty()
+        self._host_reset(args)
+
     def terminal(self):
         return bool(self._get_info()[1])
 
@@ -63,7 +115,7 @@ class DeviceEnvironment(BaseEnvironment):
         return [int(a) for a in ids[0, :n].tolist()]
 
     def action_length(self):
-        return self._env.A
+        return self._A
 
     def players(self):
         return [0, 1]

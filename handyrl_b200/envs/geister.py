@@ -21,10 +21,8 @@ class Environment(DeviceEnvironment):
     P = {-1: '_', 0: 'B', 1: 'R', 2: 'b', 3: 'r', 4: '*'}
     GOALS = (((-1, 5), (6, 5)), ((-1, 0), (6, 0)))   # geister.py:183-186
 
-    def reset(self, args={}):
+    def _host_reset(self, args):
         self.args = args
-        self._env.reset()
-        self._dirty()
         self.record = []
         self.layouts = {}
 

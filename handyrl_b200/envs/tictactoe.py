@@ -12,11 +12,6 @@ class Environment(DeviceEnvironment):
     BLACK, WHITE = 1, -1
     C = {0: '_', BLACK: 'O', WHITE: 'X'}
 
-    def reset(self, args=None):
-        self._env.reset()
-        self._dirty()
-        self.record = []
-
     # -- string protocol (tictactoe.py:86-101, 121-131) ---------------------
     def action2str(self, a, _=None):
         return self.X[a // 3] + self.Y[a % 3]

@@ -47,3 +47,17 @@ def test_no_cpu_fallback():
     v = torch.zeros(2, 3, 2, 1)
     with pytest.raises(_lib.B200RLError):
         compute_target('TD', v, v, None, 0.7, 1.0, None, None)
+
+
+def test_facades_construct_without_cuda():
+    """B1: the reference builds the environment in the parent before forking its workers (train.py:428,
+    worker.py:189): construction, players(), action_length() and net() must not touch the device."""
+    import torch
+    from handyrl_b200.environment import make_env
+    was_init = torch.cuda.is_initialized()
+    for name, A in (("TicTacToe", 9), ("ParallelTicTacToe", 9), ("Geister", 214), ("CIGeister", 214)):
+        e = make_env({"env": name, "id": 3})
+        assert e.players() == [0, 1] and e.action_length() == A
+        assert isinstance(e.net(), type)
+        assert e._engine is None
+    assert torch.cuda.is_initialized() == was_init

@@ -240,6 +240,109 @@ def gen_loss():
     print("loss_cases.pkl:", os.path.getsize(os.path.join(GOLD, "loss_cases.pkl")), "bytes")
 
 
+SELECT_CASES = [
+    # name, number of episodes, maximum_episodes, forward_steps, compress_steps, draws, seed
+    ('short_buffer', 40, 1000, 16, 4, 1500, 11),          # accept rate ~ 1 everywhere
+    ('steep', 300, 320, 8, 4, 1500, 12),                  # oldest episodes almost always rejected
+    ('overfull', 260, 200, 16, 3, 1500, 13),              # len(episodes) > maximum_episodes (train.py:286-287)
+    ('one_step_windows', 64, 100, 1, 1, 600, 14),
+    ('long_window', 50, 60, 512, 8, 600, 15),             # forward_steps > every episode
+]
+
+
+def gen_select():
+    """`Batcher.select_episode` of the reference (handyrl/train.py:284-302) called on a stub object, under
+    random.seed(s): the draws (episode index, window, blocks) pin handyrl_b200.train.select_episode, and their
+    histogram pins the law of the device / host-C window selection."""
+    import pickle
+    import random
+    from types import SimpleNamespace
+    from handyrl.train import Batcher
+    from handyrl_b200.train import select_episode
+
+    out = {}
+    for name, n_ep, max_ep, T, cs, draws, seed in SELECT_CASES:
+        rng = random.Random(seed)
+        steps = [rng.randrange(3, 203) for _ in range(n_ep)]
+        episodes = [{'args': {'id': i}, 'outcome': {0: 1, 1: -1}, 'steps': st,
+                     'moment': [(i, b) for b in range((st + cs - 1) // cs)]} for i, st in enumerate(steps)]
+        args = {'maximum_episodes': max_ep, 'forward_steps': T, 'compress_steps': cs}
+        stub = SimpleNamespace(episodes=episodes, args=args)
+        random.seed(seed)
+        ref = [Batcher.select_episode(stub) for _ in range(draws)]
+        mine_rng = random.Random(seed)
+        rows = []
+        for w in ref:
+            m = select_episode(episodes, args, mine_rng)
+            assert m == w, (name, m, w)
+            rows.append((w['args']['id'], w['start'], w['end'], w['base'], w['total'], w['moment'][0][1],
+                         len(w['moment'])))
+        out[name] = {'steps': steps, 'args': args, 'seed': seed, 'rows': np.asarray(rows, np.int32)}
+        print(name, 'ok', draws, 'draws; mean ep idx %.1f' % np.mean([r[0] for r in rows]))
+    with open(os.path.join(GOLD, "select_cases.pkl"), "wb") as f:
+        pickle.dump(out, f, protocol=4)
+
+
+def gen_sampler():
+    """The action draw of the reference's generation loop (handyrl/generation.py:48-53, util.py:61-63) on seeded
+    states: (legal list in reference order, logits, the random() number `random.choices` consumed, action)."""
+    import importlib
+    import pickle
+    import random
+    from handyrl.util import softmax
+
+    out = {}
+    for envname, n_states in (('tictactoe', 700), ('geister', 1500)):
+        mod = importlib.import_module('handyrl.envs.' + envname)
+        env = mod.Environment()
+        nprng = np.random.RandomState(31)
+        rec = dict(tape_off=[0], tape=[], legal_off=[0], legal=[], logits=[], u=[], action=[])
+        n = 0
+        random.seed(4242)
+        while n < n_states:
+            env.reset()
+            tape = []
+            while not env.terminal() and n < n_states:
+                player = env.turn()
+                # sharp and flat logits alike, as float32 like a model output (model.py:50-53)
+                p_ = (nprng.standard_normal(env.action_length()) * nprng.choice([0.1, 1.0, 4.0, 12.0])).astype(np.float32)
+                legal_actions = env.legal_actions(player)
+                action_mask = np.ones_like(p_) * 1e32
+                action_mask[legal_actions] = 0
+                p = p_ - action_mask
+                state = random.getstate()
+                action = random.choices(legal_actions, weights=softmax(p[legal_actions]))[0]
+                after = random.getstate()
+                random.setstate(state)
+                u = random.random()                       # the one number random.choices drew
+                assert random.getstate() == after
+                rec['tape_off'].append(rec['tape_off'][-1])          # state = tape so far (filled below)
+                rec['legal'] += [int(a) for a in legal_actions]
+                rec['legal_off'].append(len(rec['legal']))
+                rec['logits'].append(p_)
+                rec['u'].append(u)
+                rec['action'].append(int(action))
+                tape.append(int(action))
+                env.play(action, player)
+                n += 1
+            rec['tape'].append(tape)
+        # states are addressed as (game index, ply): replaying tape[g][:ply] reaches state (g, ply)
+        games, plies = [], []
+        for g, tape in enumerate(rec['tape']):
+            games += [g] * len(tape)
+            plies += list(range(len(tape)))
+        out[envname] = {
+            'game': np.asarray(games, np.int32), 'ply': np.asarray(plies, np.int32),
+            'tape_flat': np.asarray(sum(rec['tape'], []), np.int32),
+            'tape_off': np.cumsum([0] + [len(t) for t in rec['tape']]).astype(np.int32),
+            'legal': np.asarray(rec['legal'], np.int32), 'legal_off': np.asarray(rec['legal_off'], np.int32),
+            'logits': np.stack(rec['logits']), 'u': np.asarray(rec['u'], np.float64),
+            'action': np.asarray(rec['action'], np.int32)}
+        print(envname, n, 'states,', len(rec['tape']), 'games')
+    np.savez_compressed(os.path.join(GOLD, "sampler_cases.npz"),
+                        **{e + '.' + k: v for e, d in out.items() for k, v in d.items()})
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     os.makedirs(GOLD, exist_ok=True)
