@@ -67,9 +67,10 @@ SIGNATURES = {
     "b200rl_env_rollout": [c_int, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
                            c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr],
     "b200rl_env_step_record": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_int, c_ptr, c_i64, c_u64, c_ptr, c_i64,
-                               c_ptr, c_ptr, c_ptr],
+                               c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+    "b200rl_env_logit_slots": [c_int],
     "b200rl_env_sample_record": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_u64, c_u64, c_ptr, c_i64, c_u64, c_ptr, c_i64,
-                                 c_ptr, c_ptr, c_ptr, c_ptr],
+                                 c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "b200rl_make_batch": [c_int, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_int, c_ptr,
                           c_i64] + [c_ptr] * 14,
     "b200rl_select_windows": [c_ptr, c_i64, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_i64, c_ptr, c_i64, c_ptr],
@@ -81,7 +82,7 @@ SIGNATURES = {
 }
 
 # functions that return a value instead of a status
-_RESTYPE = {"b200rl_env_state_bytes": c_i64}
+_RESTYPE = {"b200rl_env_state_bytes": c_i64, "b200rl_env_logit_slots": c_i64}
 
 
 def lib():

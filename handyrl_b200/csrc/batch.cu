@@ -22,6 +22,40 @@ namespace {
 constexpr int BLK = 128;
 constexpr int WARPS = BLK / 32;
 
+// Net outputs recorded beside the 32-byte record of a ply (generation.py:40-57: moment['value'], moment['policy']).
+// Both side rings are slot-major like the record ring, so the plies of a training window are contiguous:
+//   logit ring [N][D][PL][LS]  the logits of the LEGAL actions only, in ascending action-id order (everything else
+//                              of moment['policy'] is logit - 1e32 = -1e32 in fp32): LS = LMAX rounded up to 4 floats,
+//                              288 B per Geister ply instead of 856 B
+//   value ring [N][D][2]       moment['value'][player] (0 where the player did not observe)
+template <class G>
+struct LogitSlots { static constexpr int value = (G::LMAX + 3) & ~3; };
+
+template <class G>
+__device__ __forceinline__ void record_net_outputs(const typename G::State& pre, int64_t i, int64_t D, uint64_t it,
+                                                   const float* __restrict__ logits, const float* __restrict__ values,
+                                                   float* logit_ring, float* value_ring) {
+    constexpr int PL = G::SIMULTANEOUS ? 2 : 1;
+    constexpr int LS = LogitSlots<G>::value;
+    const int64_t cell = i * D + (int64_t)ring_mod(it, (uint64_t)D);
+    if (logit_ring && logits) {
+        uint32_t lm[G::LW];
+        G::legal_bits(pre, lm);
+#pragma unroll
+        for (int q = 0; q < PL; ++q) {
+            const float* src = logits + (i * PL + q) * G::A;
+            float* dst = logit_ring + (cell * PL + q) * LS;
+            int r = 0;
+#pragma unroll
+            for (int w = 0; w < G::LW; ++w)
+                for (uint32_t m = lm[w]; m; m &= m - 1) dst[r++] = src[32 * w + __ffs((int)m) - 1];
+        }
+    }
+    if (value_ring && values) {
+        *reinterpret_cast<float2*>(value_ring + cell * 2) = make_float2(values[2 * i], values[2 * i + 1]);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // step + record: one ply driven by caller-chosen actions (net-in-the-loop self-play
 // or tape replay), writing the same trajectory records as k_rollout.
@@ -30,7 +64,9 @@ template <class G>
 __global__ void __launch_bounds__(BLK)
 k_step_record(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, const int32_t* __restrict__ sel,
               const int32_t* __restrict__ both, int auto_reset, uint4* traj, int64_t D, uint64_t it,
-              int32_t* ep_table, int64_t E, unsigned long long* counters, uint8_t* __restrict__ out_terminal) {
+              int32_t* ep_table, int64_t E, unsigned long long* counters, uint8_t* __restrict__ out_terminal,
+              const float* __restrict__ logits, const float* __restrict__ values, float* logit_ring,
+              float* value_ring) {
     const int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
     if (i >= N) return;
     typename G::State s = G::load(state, N, i);
@@ -45,6 +81,7 @@ k_step_record(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, c
     const int selp = sel ? sel[i] : 0;
     uint32_t rec[8];
     G::pack_record(s, rec);
+    record_net_outputs<G>(s, i, D, it, logits, values, logit_ring, value_ring);
     G::step(s, a, selp);
     const bool term = G::terminal(s);
     float o0 = 0.f, o1 = 0.f;
@@ -76,7 +113,7 @@ k_step_record(uint32_t* state, int64_t N, const int32_t* __restrict__ actions, c
 // (handyrl/generation.py:48-61).  For every game: legal_actions in the reference's list
 // order, p = logits[legal] (the 1e32 mask only removes the others), weights = softmax(p)
 // as util.py:61-63 (fp32 exp(p - max) / sum), then random.choices' rule: cumulative weights
-// accumulated in double, first index whose cumulative weight exceeds u * total.  The chosen
+// accumulated as fp32 (they are numpy float32 scalars), first index whose cumulative weight exceeds u * total.  The chosen
 // action is applied and recorded exactly like k_step_record.
 // ---------------------------------------------------------------------------
 template <class G>
@@ -86,16 +123,35 @@ __device__ __forceinline__ int sample_from_logits(const typename G::State& s, co
     if (n <= 0) return -1;
     float m = -INFINITY;
     for (int k = 0; k < n; ++k) m = fmaxf(m, lg[ids[k]]);
+    // x.sum() of util.py:63 is numpy's pairwise sum: sequential below 8 terms, else 8 interleaved partial sums
+    // combined as a tree and the n % 8 tail added one by one (n <= LMAX < 128: no recursion)
+    auto ex = [&](int k) { return expf(__fsub_rn(lg[ids[k]], m)); };
     float sum = 0.f;
-    for (int k = 0; k < n; ++k) sum = __fadd_rn(sum, expf(__fsub_rn(lg[ids[k]], m)));
-    double total = 0.0;
-    for (int k = 0; k < n; ++k) total += (double)__fdiv_rn(expf(__fsub_rn(lg[ids[k]], m)), sum);
-    const double x = u * total;
-    double cum = 0.0;
+    if (n < 8) {
+        for (int k = 0; k < n; ++k) sum = __fadd_rn(sum, ex(k));
+    } else {
+        float r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = ex(j);
+        int i = 8;
+        for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) r[j] = __fadd_rn(r[j], ex(i + j));
+        }
+        sum = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
+                        __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
+        for (; i < n; ++i) sum = __fadd_rn(sum, ex(i));
+    }
+    // random.choices: cum_weights = list(accumulate(weights)) over numpy float32 scalars = an fp32 running sum;
+    // total = cum_weights[-1]; population[bisect(cum_weights, random() * total, 0, n - 1)]
+    float total = 0.f;
+    for (int k = 0; k < n; ++k) total = __fadd_rn(total, __fdiv_rn(ex(k), sum));
+    const double x = u * (double)total;
+    float cum = 0.f;
     int pick = n - 1;
-    for (int k = 0; k < n; ++k) {
-        cum += (double)__fdiv_rn(expf(__fsub_rn(lg[ids[k]], m)), sum);
-        if (x < cum) { pick = k; break; }   // bisect_right(cum_weights, x)
+    for (int k = 0; k < n - 1; ++k) {
+        cum = __fadd_rn(cum, __fdiv_rn(ex(k), sum));
+        if (x < (double)cum) { pick = k; break; }   // bisect_right(cum_weights, x, 0, n - 1)
     }
     return ids[pick];
 }
@@ -105,7 +161,8 @@ __global__ void __launch_bounds__(BLK)
 k_sample_record(uint32_t* state, int64_t N, const float* __restrict__ logits, const double* __restrict__ u_in,
                 uint64_t seed, uint64_t game_id_base, uint4* traj, int64_t D, uint64_t it, int32_t* ep_table,
                 int64_t E, unsigned long long* counters, int32_t* __restrict__ out_action,
-                uint8_t* __restrict__ out_terminal) {
+                uint8_t* __restrict__ out_terminal, const float* __restrict__ values, float* logit_ring,
+                float* value_ring) {
     const int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x;
     if (i >= N) return;
     typename G::State s = G::load(state, N, i);
@@ -129,6 +186,7 @@ k_sample_record(uint32_t* state, int64_t N, const float* __restrict__ logits, co
     const bool first = G::steps(s) == 0;
     uint32_t rec[8];
     G::pack_record(s, rec);
+    if (traj) record_net_outputs<G>(s, i, D, it, logits, values, logit_ring, value_ring);
     G::step(s, a, selp);
     const bool term = G::terminal(s);
     float o0 = 0.f, o1 = 0.f;
@@ -170,8 +228,8 @@ enum { MB_TURN = 0, MB_ALL = 1, MB_SOLO = 2 };
 struct BatchParams {
     const uint4* traj;
     int64_t D, N;
-    const float* values;  // [D][N][2] value estimates recorded with the ring, or null (RandomModel: 0)
-    const float* logits;  // [D][N][A] behaviour logits, or null (RandomModel: zero logits)
+    const float* values;  // [N][D][2] value estimates recorded with the ring, or null (RandomModel: 0)
+    const float* logits;  // [N][D][PL][LS] logits of the legal actions, or null (RandomModel: zero logits)
     const int32_t* win;   // [B][8] = slot, it_lo, it_hi, len, st, total, wincode, solo player
     const float* ret_table;  // discounted return of a ply with m plies left, m = 0..ret_len-1
     int ret_len;
@@ -284,7 +342,7 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
                 const bool is_turn = parallel || pl == tp;
                 const bool observed = is_turn || p.obs_all;
                 float v = 0.f;
-                if (observed && p.values) v = p.values[((int64_t)ring_mod(it, (uint64_t)p.D) * p.N + slot) * 2 + pl];
+                if (observed && p.values) v = p.values[(slot * p.D + (int64_t)ring_mod(it, (uint64_t)p.D)) * 2 + pl];
                 val[q] = v;
                 rew[q] = G::HAS_REWARD ? G::reward(s) : 0.f;
                 const int left = total - (stt + t);
@@ -367,26 +425,47 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
 }
 
 // policy = logits - action_mask for recorded behaviour logits (generation.py:52): one warp per
-// (cell, player) row; rows without any legal action (padding, non-turn players) stay zero.
+// (cell, player) row; rows without any legal action (padding, non-turn players) stay zero.  The ring holds the
+// legal logits in ascending action-id order: entry a of a legal action is its rank among the legal bits, found
+// with a ballot per 32 actions; an illegal entry is logit - 1e32 = -1e32 for any logit below 4.8e24.
 template <class G>
 __global__ void __launch_bounds__(BLK) k_policy_from_logits(const BatchParams p) {
+    constexpr int PL = G::SIMULTANEOUS ? 2 : 1;
+    constexpr int LS = LogitSlots<G>::value;
     const int Po = p.mode == MB_ALL ? 2 : 1;
     const int lane = threadIdx.x & 31;
     const int64_t rows = p.B * p.T * Po;
     const int64_t r = blockIdx.x * (int64_t)WARPS + (threadIdx.x >> 5);
     if (r >= rows) return;
     const int64_t c = r / Po;
+    const int q = (int)(r - c * Po);
     const int64_t b = c / p.T;
     const int t = (int)(c - b * p.T);
     const int32_t* w = p.win + b * 8;
-    bool any = false;
-    for (int a = lane; a < G::A; a += 32) any |= p.amask[r * G::A + a] == 0.f;
-    any = __any_sync(0xffffffffu, any);
-    const bool live = t < w[3] && any;
+    // the player this row describes; only simultaneous games record one logit row per player
+    const int pl = PL == 1 ? 0 : (p.mode == MB_TURN ? 0 : (p.mode == MB_SOLO ? (w[7] & 1) : q));
     const uint64_t it = ((uint64_t)(uint32_t)w[1] | ((uint64_t)(uint32_t)w[2] << 32)) + (uint64_t)t;
-    const float* lg = p.logits + ((int64_t)ring_mod(it, (uint64_t)p.D) * p.N + w[0]) * G::A;
-    for (int a = lane; a < G::A; a += 32)
-        p.policy[r * G::A + a] = live ? __fsub_rn(lg[a], p.amask[r * G::A + a]) : 0.f;
+    const float* lg = p.logits + (((int64_t)w[0] * p.D + (int64_t)ring_mod(it, (uint64_t)p.D)) * PL + pl) * LS;
+    const bool in_window = t < w[3];
+    int base = 0;
+    float out[(G::A + 31) / 32];
+    bool any = false;
+#pragma unroll
+    for (int j = 0; j < (G::A + 31) / 32; ++j) {
+        const int a = j * 32 + lane;
+        const bool legal = a < G::A && p.amask[r * G::A + a] == 0.f;
+        const uint32_t bits = __ballot_sync(0xffffffffu, legal);
+        const int rank = base + __popc(bits & ((1u << lane) - 1u));
+        out[j] = (legal && in_window) ? lg[rank] : -1e32f;
+        base += __popc(bits);
+        any |= bits != 0u;
+    }
+    const bool live = in_window && any;
+#pragma unroll
+    for (int j = 0; j < (G::A + 31) / 32; ++j) {
+        const int a = j * 32 + lane;
+        if (a < G::A) p.policy[r * G::A + a] = live ? out[j] : 0.f;
+    }
 }
 
 // Ragged -> padded stack for host-decoded reference episodes: out[b][t][:] = src[off[b]+t][:]
@@ -490,24 +569,33 @@ int launch_make_batch(const BatchParams& p, cudaStream_t stream) {
             return B200RL_ERR_ARG;                                                      \
     }
 
+extern "C" int64_t b200rl_env_logit_slots(int game) {
+    DISPATCH_GAME(game, return LogitSlots<G>::value);
+    return -1;
+}
+
 extern "C" int b200rl_env_step_record(int game, void* state, int64_t N, const int32_t* actions,
                                       const int32_t* selected, const int32_t* both, int auto_reset, void* traj,
                                       int64_t D, uint64_t it, int32_t* ep_table, int64_t E, uint64_t* counters,
-                                      uint8_t* out_terminal, void* stream) {
+                                      uint8_t* out_terminal, const float* logits, const float* values,
+                                      float* logit_ring, float* value_ring, void* stream) {
+    B200RL_REQUIRE(!value_ring || ((uintptr_t)value_ring % 8) == 0, "env_step_record: value ring must be 8-byte aligned");
     B200RL_REQUIRE(state && actions && traj && D >= 1, "env_step_record: null state/actions/traj or D < 1");
     B200RL_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)traj % 32) == 0, "env_step_record: 16-byte alignment");
     B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_step_record: episode table needs E >= 1 and counters");
     if (N <= 0) return B200RL_OK;
     DISPATCH_GAME(game, (k_step_record<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(
                             (uint32_t*)state, N, actions, selected, both, auto_reset, (uint4*)traj, D, it, ep_table,
-                            E, (unsigned long long*)counters, out_terminal)));
+                            E, (unsigned long long*)counters, out_terminal, logits, values, logit_ring, value_ring)));
     return b200rl_check_launch("k_step_record");
 }
 
 extern "C" int b200rl_env_sample_record(int game, void* state, int64_t N, const float* logits, const double* u,
                                         uint64_t seed, uint64_t game_id_base, void* traj, int64_t D, uint64_t it,
                                         int32_t* ep_table, int64_t E, uint64_t* counters, int32_t* out_action,
-                                        uint8_t* out_terminal, void* stream) {
+                                        uint8_t* out_terminal, const float* values, float* logit_ring,
+                                        float* value_ring, void* stream) {
+    B200RL_REQUIRE(!value_ring || ((uintptr_t)value_ring % 8) == 0, "env_sample_record: value ring must be 8-byte aligned");
     B200RL_REQUIRE(state && logits, "env_sample_record: null state/logits");
     B200RL_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)traj % 32) == 0, "env_sample_record: 16-byte alignment");
     B200RL_REQUIRE(!traj || D >= 1, "env_sample_record: trajectory ring depth D must be >= 1");
@@ -515,7 +603,7 @@ extern "C" int b200rl_env_sample_record(int game, void* state, int64_t N, const 
     if (N <= 0) return B200RL_OK;
     DISPATCH_GAME(game, (k_sample_record<G><<<grid_for(N), BLK, 0, (cudaStream_t)stream>>>(
                             (uint32_t*)state, N, logits, u, seed, game_id_base, (uint4*)traj, D, it, ep_table, E,
-                            (unsigned long long*)counters, out_action, out_terminal)));
+                            (unsigned long long*)counters, out_action, out_terminal, values, logit_ring, value_ring)));
     return b200rl_check_launch("k_sample_record");
 }
 

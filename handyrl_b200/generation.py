@@ -32,8 +32,14 @@ class TrajectoryStore:
         self.E = int(max_episodes)
         self.ep_table = torch.zeros(self.E, 4, dtype=torch.int32, device=dev)
         self.counters = torch.zeros(8, dtype=torch.int64, device=dev)
-        self.values = torch.zeros(self.D, self.N, 2, dtype=torch.float32, device=dev) if record_values else None
-        self.logits = torch.zeros(self.D, self.N, env.A, dtype=torch.float32, device=dev) if record_logits else None
+        # net outputs beside the records, slot-major too: values [N][D][2]; logits [N][D][PL][LS] = the logits of
+        # the legal actions only (ascending action id), LS = longest legal list rounded up to 4 floats
+        # (288 B per Geister ply instead of the 856 B of a full row; see include/b200rl.h)
+        self.PL = 2 if env.game == 1 else 1
+        self.LS = int(_lib.lib().b200rl_env_logit_slots(env.game))
+        self.values = torch.zeros(self.N, self.D, 2, dtype=torch.float32, device=dev) if record_values else None
+        self.logits = (torch.zeros(self.N, self.D, self.PL, self.LS, dtype=torch.float32, device=dev)
+                       if record_logits else None)
         self.it = 0            # next ring iteration to be written
         self._ep_read = 0      # episode-table cursor already handed out
 
@@ -127,6 +133,21 @@ def _map(x, fn):
     return fn(x) if x is not None else None
 
 
+def _zip(a, b, fn):
+    """zip-map over two nested containers of the same structure"""
+    if isinstance(a, (list, tuple)):
+        return type(a)(_zip(x, y, fn) for x, y in zip(a, b))
+    if isinstance(a, dict):
+        return {k: _zip(a[k], b[k], fn) for k in a}
+    return fn(a, b) if a is not None else None
+
+
+def _set_player(h, rows, player, new):
+    """h (N, 2, ...) with h[n, player[n]] <- new[n]"""
+    h[rows, player] = new.to(h.dtype)      # in place (play() runs under no_grad on its own copy)
+    return h
+
+
 class BatchGenerator:
     """N concurrent self-play games on one GPU (one process per GPU; shard by `game_id_base`)."""
 
@@ -147,21 +168,33 @@ class BatchGenerator:
         st.it = self.env.it
 
     # -- caller-chosen actions (policy network in PyTorch, tape replay) -------------
+    def _net_outputs(self, values, logits):
+        """(values (N,2), logits (N,PL,A)) as contiguous fp32 CUDA tensors when the store records them, else None."""
+        env, st = self.env, self.store
+        v = l = None
+        if st.values is not None and values is not None:
+            v = torch.as_tensor(values, dtype=torch.float32, device=env.device).reshape(env.N, 2).contiguous()
+        if st.logits is not None and logits is not None:
+            l = torch.as_tensor(logits, dtype=torch.float32, device=env.device)
+            if l.numel() != env.N * st.PL * env.A:
+                raise _lib.B200RLError("logits must have shape (N, %s%d)" % ("2, " if st.PL == 2 else "", env.A))
+            l = l.contiguous()
+        return v, l
+
     def step(self, actions, selected=None, both=None, values=None, logits=None, auto_reset=True):
-        """One recorded ply.  actions (N,) int32, <0 = slot idle.  `values` (N,2) / `logits` (N,A)
-        are stored beside the ring when the store records them.  Returns terminal (N,) uint8."""
+        """One recorded ply.  actions (N,) int32, <0 = slot idle (only allowed between episodes: an idle ply
+        inside an episode would leave a hole in the ring).  `values` (N,2) / `logits` (N,A) [(N,2,A) for
+        ParallelTicTacToe] are recorded beside the ring by the kernel when the store keeps them.
+        Returns terminal (N,) uint8."""
         env, st = self.env, self.store
         a, s, b = env._i32(actions), env._i32(selected), env._i32(both)
-        k = st.it % st.D
-        if st.values is not None and values is not None:
-            st.values[k].copy_(values)
-        if st.logits is not None and logits is not None:
-            st.logits[k].copy_(logits)
+        v, l = self._net_outputs(values, logits)
         term = torch.empty(env.N, dtype=torch.uint8, device=env.device)
         with torch.cuda.device(env.device):
             _lib.call("b200rl_env_step_record", env.game, env._st(), env.N, _ptr(a), _ptr(s), _ptr(b),
                       1 if auto_reset else 0, _ptr(st.traj), st.D, st.it, _ptr(st.ep_table), st.E,
-                      _ptr(st.counters), _ptr(term), env._stream())
+                      _ptr(st.counters), _ptr(term), _ptr(l), _ptr(v), _ptr(st.logits), _ptr(st.values),
+                      env._stream())
         st.it += 1
         env.it = st.it
         return term
@@ -173,22 +206,15 @@ class BatchGenerator:
         return self.env.step_observe(None, auto_reset=True, out=out)
 
     def act(self, logits, values=None, u=None, out_action=None):
-        """Sample one action per game from `logits` (N, A) [(N, 2, A) for ParallelTicTacToe] like
-        generation.py:48-53, apply and record it.  `values` (N, 2) are stored beside the ring when the store
-        records them.  Returns (actions (N, PL) int32, terminal (N,) uint8)."""
+        """Sample one action per game from `logits` (N, A) [(N, 2, A) for ParallelTicTacToe: one row per player]
+        like generation.py:48-53, apply and record it.  The legal logits and `values` (N, 2) are recorded beside
+        the ring by the same kernel when the store keeps them.  Returns (actions (N, PL) int32, terminal (N,) uint8)."""
         env, st = self.env, self.store
-        N = env.N
-        PL = 2 if env.game == 1 else 1
+        N, PL = env.N, st.PL
         if not (logits.is_cuda and logits.dtype == torch.float32 and logits.numel() == N * PL * env.A):
             raise _lib.B200RLError("act: logits must be CUDA float32 of shape (N, %s%d)" % ("2, " if PL == 2 else "", env.A))
         logits = logits.contiguous()
-        k = st.it % st.D
-        if st.logits is not None:
-            # the ring keeps the turn player's logits; for simultaneous games player 0's row (SOLO batches of
-            # ParallelTicTacToe re-derive the policy per player from the record, RandomModel-style)
-            st.logits[k].copy_(logits.view(N, PL, env.A)[:, 0])
-        if st.values is not None and values is not None:
-            st.values[k].copy_(values.reshape(N, 2))
+        v, _ = self._net_outputs(values, None)
         if u is not None:
             u = u.to(device=env.device, dtype=torch.float64).contiguous()
         act = out_action if out_action is not None else torch.empty(N, PL, dtype=torch.int32, device=env.device)
@@ -196,18 +222,37 @@ class BatchGenerator:
         with torch.cuda.device(env.device):
             _lib.call("b200rl_env_sample_record", env.game, env._st(), N, _ptr(logits), _ptr(u), self.seed,
                       self.game_id_base, _ptr(st.traj), st.D, st.it, _ptr(st.ep_table), st.E, _ptr(st.counters),
-                      _ptr(act), _ptr(term), env._stream())
+                      _ptr(act), _ptr(term), _ptr(v), _ptr(st.logits), _ptr(st.values), env._stream())
         st.it += 1
         env.it = st.it
         return act, term
 
+    def init_hidden(self, model):
+        """Per-PLAYER recurrent state of all games, leaves shaped (N, 2, ...) - the reference keeps
+        `hidden[player]` for every player of a game (generation.py:24-26).  None for feed-forward nets."""
+        if not hasattr(model, 'init_hidden'):
+            return None
+        h = model.init_hidden([self.env.N, 2])
+        return _map(h, lambda t: t.to(self.env.device)) if h is not None else None
+
     @torch.no_grad()
     def play(self, model, n_plies, hidden=None):
         """n_plies plies of self-play for all games with `model(obs, hidden) -> {'policy','value'[,'hidden']}`
-        evaluated on the device (one forward per ply for all N games).  Recurrent state is zeroed for games that
-        restart.  Returns the final hidden state."""
-        env = self.env
+        evaluated on the device (one forward per ply for all N games; `observation: False` semantics: only the
+        acting players observe, generation.py:36-41).
+
+        `hidden` is the per-player state of `init_hidden` (leaves (N, 2, ...)).  Like the reference's
+        `hidden[player]` (generation.py:24-26, 39-41), a player's state advances only on the plies that player
+        observes: each ply the turn player's slice is gathered, fed to the net, and the new state is scattered
+        back into that slice alone; both slices are zeroed when a game restarts.  This is the recurrent context
+        `forward_prediction` rebuilds from the batch in training (train.py:160-175), so the recorded behaviour
+        logits and values are what the learner's network would produce at the same weights.
+        Returns the final hidden state."""
+        env, st = self.env, self.store
+        N = env.N
+        simultaneous = st.PL == 2
         out = None
+        rows = torch.arange(N, device=env.device)
         for _ in range(int(n_plies)):
             out = self.observe_turn(out)
             if env.scalar_shape is not None:
@@ -217,15 +262,29 @@ class BatchGenerator:
             if hidden is not None:
                 fresh = (out['terminal'] != 0)   # slots restarted by observe_turn
                 hidden = _map(hidden, lambda h: h * (~fresh).view(-1, *([1] * (h.dim() - 1))).to(h.dtype))
-            o = model(obs, hidden)
-            hidden = o.get('hidden', None)
-            v = o.get('value')
-            values = None
-            if v is not None and self.store.values is not None:
-                # the net evaluates the turn player's view: store it in that player's slot (generation.py:40-44)
-                turn = out['turn'].long().view(-1, 1)
-                values = torch.zeros(env.N, 2, device=env.device).scatter_(1, turn, v.view(env.N, 1).float())
-            self.act(o['policy'].float(), values=values)
+            if simultaneous:
+                # both players act every ply (parallel_tictactoe.py:20-29) on their own view and state
+                pol, val = [], []
+                for q in (0, 1):
+                    o = model(obs, _map(hidden, lambda h: h[:, q]) if hidden is not None else None)
+                    if hidden is not None and o.get('hidden') is not None:
+                        hidden = _zip(hidden, o['hidden'], lambda h, nh: _set_player(h, rows, q, nh))
+                    pol.append(o['policy'].float())
+                    val.append(o['value'].float().view(N) if o.get('value') is not None else None)
+                logits = torch.stack(pol, dim=1)
+                values = torch.stack(val, dim=1) if val[0] is not None and st.values is not None else None
+            else:
+                turn = out['turn'].long()
+                o = model(obs, _map(hidden, lambda h: h[rows, turn]) if hidden is not None else None)
+                if hidden is not None and o.get('hidden') is not None:
+                    hidden = _zip(hidden, o['hidden'], lambda h, nh: _set_player(h, rows, turn, nh))
+                logits = o['policy'].float()
+                v = o.get('value')
+                values = None
+                if v is not None and st.values is not None:
+                    # the net evaluates the turn player's view: store it in that player's slot (generation.py:40-44)
+                    values = torch.zeros(N, 2, device=env.device).index_put_((rows, turn), v.view(N).float())
+            self.act(logits, values=values)
         return hidden
 
     # -- window selection on the device (Batcher.select_episode, train.py:284-302) -------

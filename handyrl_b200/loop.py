@@ -47,7 +47,7 @@ class ActorLearner:
                                   depth=depth, max_episodes=1 << 20, record_values=True, record_logits=True)
         self.learner = DataParallelLearner(self.net, args)
         self.n_games = n_games
-        self.hidden = self._init_hidden([n_games])
+        self.hidden = self.gen.init_hidden(self.net)      # per player: (n_games, 2, ...)
         self.batch = None
         self.simultaneous = env_name == 'ParallelTicTacToe'
 
@@ -60,14 +60,7 @@ class ActorLearner:
     @torch.no_grad()
     def generate(self, plies):
         self.net.eval()
-        if self.simultaneous:
-            # both players act on the same observation in this game (parallel_tictactoe.py:54-58 quirk)
-            for _ in range(plies):
-                out = self.gen.observe_turn()
-                o = self.net(out['main'], None)
-                self.gen.act(o['policy'].float().unsqueeze(1).expand(-1, 2, -1).contiguous())
-        else:
-            self.hidden = self.gen.play(self.net, plies, self.hidden)
+        self.hidden = self.gen.play(self.net, plies, self.hidden)
 
     def train(self, steps):
         a = self.args

@@ -195,24 +195,41 @@ int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_plies, uint64
  * does not move.  `both` (N,2) carries both players' chosen actions for
  * ParallelTicTacToe (make_batch needs them), else NULL.  With auto_reset a finished
  * game is restarted before the ply (generation.py:27).
+ *
+ * Net outputs of the ply (generation.py:40-57: moment['policy'], moment['value']) are recorded beside the
+ * record when both the input and its ring are given (all four may be NULL):
+ *   logits     (N, PL, A) fp32, PL = 2 for ParallelTicTacToe else 1: the acting player's raw logits
+ *   values     (N, 2) fp32: moment['value'][player], 0 where a player did not observe
+ *   logit_ring [N][D][PL][LS] fp32, slot-major like the record ring; LS = b200rl_env_logit_slots(game).  Only the
+ *              logits of the LEGAL actions are kept, in ascending action-id order: every other entry of
+ *              moment['policy'] = logits - action_mask is -1e32 in fp32 whatever the logit
+ *   value_ring [N][D][2] fp32
  */
 int b200rl_env_step_record(int game, void* state, int64_t N, const int32_t* actions, const int32_t* selected,
                            const int32_t* both, int auto_reset, void* traj, int64_t D, uint64_t it,
-                           int32_t* ep_table, int64_t E, uint64_t* counters, uint8_t* out_terminal, void* stream);
+                           int32_t* ep_table, int64_t E, uint64_t* counters, uint8_t* out_terminal,
+                           const float* logits, const float* values, float* logit_ring, float* value_ring,
+                           void* stream);
+
+/* Floats per (ply, acting player) of the logit ring: the longest legal list (tictactoe.py:149-151: 9;
+ * geister.py:472-486: the 70 setup actions) rounded up to a multiple of 4.  -1 for an unknown game. */
+int64_t b200rl_env_logit_slots(int game);
 
 /*
  * The acting half of one self-play ply with a real policy (generation.py:48-61) for N games:
  * restart finished games, take legal_actions in the reference's list order, weights =
- * softmax(logits[legal]) (util.py:61-63), draw like random.choices (cumulative weights in double,
- * first index whose cumulative weight exceeds u * total), apply the action, write the trajectory
- * record / episode table / counters like b200rl_env_step_record.
+ * softmax(logits[legal]) (util.py:61-63, numpy's pairwise fp32 sum), draw like random.choices (cumulative
+ * weights as an fp32 running sum - they are numpy float32 scalars -, first index whose cumulative weight
+ * exceeds u * total), apply the action, write the trajectory record / episode table / counters and the
+ * logit / value rings like b200rl_env_step_record (values, logit_ring, value_ring may be NULL).
  *   logits (N, PL, A) fp32, PL = 2 for ParallelTicTacToe (both players act, parallel_tictactoe.py:20-29) else 1
  *   u      (N, PL) doubles in [0,1) or NULL (counter RNG keyed (seed, game_id_base + slot, it))
  *   out_action (N, PL) int32, out_terminal (N) uint8; either may be NULL; traj may be NULL
  */
 int b200rl_env_sample_record(int game, void* state, int64_t N, const float* logits, const double* u, uint64_t seed,
                              uint64_t game_id_base, void* traj, int64_t D, uint64_t it, int32_t* ep_table, int64_t E,
-                             uint64_t* counters, int32_t* out_action, uint8_t* out_terminal, void* stream);
+                             uint64_t* counters, int32_t* out_action, uint8_t* out_terminal, const float* values,
+                             float* logit_ring, float* value_ring, void* stream);
 
 enum { B200RL_BATCH_TURN = 0, B200RL_BATCH_ALL = 1, B200RL_BATCH_SOLO = 2 };
 
@@ -220,8 +237,8 @@ enum { B200RL_BATCH_TURN = 0, B200RL_BATCH_ALL = 1, B200RL_BATCH_SOLO = 2 };
  * make_batch(episodes, args) (handyrl/train.py:33-133) over windows of the device
  * trajectory ring.
  *   traj     : [N][D] x 32 B slot-major ring written by b200rl_env_rollout / b200rl_env_step_record
- *   values   : [D][N][2] fp32 value estimates recorded beside the ring, or NULL (RandomModel: 0)
- *   logits   : [D][N][A] fp32 behaviour logits, or NULL (RandomModel: zero logits)
+ *   values   : [N][D][2] fp32 value ring of b200rl_env_step_record, or NULL (RandomModel: 0)
+ *   logits   : [N][D][PL][LS] fp32 logit ring of b200rl_env_step_record, or NULL (RandomModel: zero logits)
  *   windows  : (B,8) int32 {slot, first_it lo, first_it hi, len = end-start, start, total steps,
  *              winner code, solo player}; first_it is the ring iteration of ply `start`
  *   T        : args['forward_steps']; rows t >= len are padded exactly like train.py:92-104

@@ -76,7 +76,7 @@ def replay_and_compare(env_key, t):
 
 @pytest.mark.parametrize("env_key", list(ENVS))
 def test_reference_tapes(golden_dir, env_key):
-    t = np.load(os.path.join(golden_dir, "tape_%s.npz" % env_key))
+    t = dict(np.load(os.path.join(golden_dir, "tape_%s.npz" % env_key)))   # NpzFile re-inflates on every access
     replay_and_compare(env_key, dict(t))
 
 

@@ -15,7 +15,7 @@ def _bits(a, n):
 
 @pytest.mark.parametrize("env", ENVS)
 def test_c_oracle_replays_reference_tapes(golden_dir, env):
-    t = np.load(os.path.join(golden_dir, "tape_%s.npz" % env))
+    t = dict(np.load(os.path.join(golden_dir, "tape_%s.npz" % env)))   # NpzFile re-inflates on every access
     geister = 'geister' in env
     nmain = 252 if geister else 27
     e = games_c.Env(env)

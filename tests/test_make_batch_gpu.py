@@ -1,6 +1,7 @@
 """GPU parity of make_batch: the device path (trajectory ring -> b200rl_make_batch) against
 (1) golden outputs of the reference's make_batch on the same episodes and windows, and
 (2) the numpy oracle on episodes exported from a device rollout.  Bar: bit-exact."""
+import bz2
 import os
 import pickle
 import random
@@ -36,16 +37,23 @@ def _flatten(batch):
 
 
 def replay_tapes(env_key, tapes):
-    """slot g replays episode g; returns the generator and device episodes"""
+    """slot g replays episode g; returns the generator and device episodes.  Tapes that carry the net outputs
+    of every ply ('values' (steps,2), 'logits' (steps,PL,A)) fill the value / logit rings as well."""
     from handyrl_b200.generation import BatchGenerator, DeviceMoments
     G = len(tapes)
     L = max(t['steps'] for t in tapes)
-    gen = BatchGenerator(ENVS[env_key], G, depth=L + 2)
+    net = 'values' in tapes[0]
+    gen = BatchGenerator(ENVS[env_key], G, depth=L + 2, record_values=net, record_logits=net)
     for k in range(L):
         act = np.array([t['actions'][k] if k < t['steps'] else -1 for t in tapes], np.int32)
         sel = np.array([t['sel'][k] if k < t['steps'] else 0 for t in tapes], np.int32)
         both = np.array([t['both'][k] if k < t['steps'] else [0, 0] for t in tapes], np.int32)
-        gen.step(act, sel, both, auto_reset=False)
+        values = logits = None
+        if net:
+            values = np.stack([t['values'][k] if k < t['steps'] else np.zeros(2, np.float32) for t in tapes])
+            z = np.zeros_like(tapes[0]['logits'][0])
+            logits = np.stack([t['logits'][k] if k < t['steps'] else z for t in tapes])
+        gen.step(act, sel, both, values=values, logits=logits, auto_reset=False)
     eps = [{'args': {}, 'steps': t['steps'], 'outcome': {0: t['outcome'][0], 1: t['outcome'][1]},
             'moment': DeviceMoments(gen.store, g, 0, t['steps'])} for g, t in enumerate(tapes)]
     return gen, eps
@@ -69,6 +77,42 @@ def test_device_make_batch_matches_reference(cases, name):
         np.testing.assert_array_equal(out[k], ref, err_msg=k)
 
 
+NET_CASES = ['ttt_net_turn', 'ttt_net_all', 'pttt_net_solo', 'geister_net_turn', 'geister_net_all']
+
+
+@pytest.fixture(scope="module")
+def net_cases(golden_dir):
+    with open(os.path.join(golden_dir, "net_batch_cases.pkl.bz2"), "rb") as f:
+        return pickle.loads(bz2.decompress(f.read()))
+
+
+@pytest.mark.parametrize("name", NET_CASES)
+def test_device_make_batch_with_recorded_net_outputs_matches_reference(net_cases, name):
+    """A12 with a network in the loop (generation.py:36-57 -> train.py:60-82): the value ring read and
+    k_policy_from_logits against the reference's Generator + make_batch run with a seeded reference net."""
+    from handyrl_b200.train import make_batch
+    c = net_cases[name]
+    gen, eps = replay_tapes(c['env'], c['tapes'])
+    wins = [{'args': {}, 'outcome': eps[i]['outcome'], 'moment': eps[i]['moment'], 'base': 0, 'start': st,
+             'end': ed, 'total': tot} for i, st, ed, tot in c['windows']]
+    random.seed(c['seed'])
+    out = _flatten(make_batch(wins, c['args']))
+    assert set(out) == set(c['out'])
+    for k, ref in c['out'].items():
+        assert out[k].shape == ref.shape and out[k].dtype == ref.dtype, (k, out[k].shape, ref.shape, out[k].dtype)
+        np.testing.assert_array_equal(out[k], ref, err_msg=k)
+
+
+@pytest.mark.parametrize("name", NET_CASES)
+def test_reference_format_episodes_with_net_outputs_match_reference(net_cases, name):
+    from handyrl_b200.train import make_batch
+    c = net_cases[name]
+    random.seed(c['seed'])
+    out = _flatten(make_batch(c['ep_minimum'], c['args']))
+    for k, ref in c['out'].items():
+        np.testing.assert_array_equal(out[k], ref, err_msg=k)
+
+
 @pytest.mark.parametrize("game,tbt,obs", [('Geister', True, False), ('Geister', True, True), ('TicTacToe', True, False),
                                           ('CIGeister', False, False)])
 def test_rollout_export_roundtrip_against_oracle(game, tbt, obs):
@@ -88,14 +132,28 @@ def test_rollout_export_roundtrip_against_oracle(game, tbt, obs):
     dev_w = [select_episode(eps, args, rng) for _ in range(16)]
     rng.setstate(state)
     ref_w = [select_episode(ref_eps, args, rng) for _ in range(16)]
-    if obs:
-        # exported episodes carry turn-player moments only (observation=False generation); the
-        # observation=True batch is compared on the turn player's rows
-        pytest.skip("covered by the golden cases")
     random.seed(9)
     out = _flatten(make_batch(dev_w, args))
     random.seed(9)
     ref = make_batch_np.make_batch(ref_w, args)
+    if obs:
+        # The exported episodes were generated with observation=False: their non-turn moments are None, which the
+        # reference's ALL mode pads (zero observation, omask 0), while the device re-encodes the non-turn player's
+        # view from the record (omask 1, what observation=True generation yields - pinned by the golden *_all
+        # cases).  On the turn player's rows, and for every per-ply scalar, the two must agree bit for bit.
+        tm = ref['turn_mask'][..., 0] == 1                                  # (B, T, P)
+        assert np.array_equal(out['turn_mask'], ref['turn_mask'])
+        for k in ref:
+            if k == 'observation_mask':
+                live = ref['episode_mask'][:, :, 0, 0] == 1
+                assert np.all(out[k][live] == 1) and np.all(out[k][~live] == 0)
+            elif k.startswith('observation.') or k in ('policy', 'action_mask', 'action'):
+                np.testing.assert_array_equal(out[k][tm], ref[k][tm], err_msg=k)
+                if k.startswith('observation.'):                            # the reference's padding of None
+                    assert not ref[k][~tm].any()
+            else:
+                np.testing.assert_array_equal(out[k], ref[k], err_msg=k)
+        return
     for k in ref:
         np.testing.assert_array_equal(out[k], ref[k], err_msg=k)
 

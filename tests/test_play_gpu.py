@@ -63,10 +63,9 @@ def test_play_with_network_feeds_make_batch(game):
     torch.manual_seed(0)
     net = (nets.GeisterNet() if game == 'Geister' else nets.SimpleConv2dModel()).cuda().eval()
     gen = BatchGenerator(game, N, seed=9, depth=512, max_episodes=1 << 14, record_values=True, record_logits=True)
-    hidden = None
-    if game == 'Geister':
-        hidden = net.init_hidden([N])
-        hidden = tuple([t.cuda() for t in part] for part in hidden)
+    assert gen.store.logits.shape == (N, 512, 1, 72 if game == 'Geister' else 12)
+    hidden = gen.init_hidden(net)          # per player: leaves (N, 2, ...); None for the feed-forward net
+    assert (hidden is None) == (game != 'Geister')
     plies = 260 if game == 'Geister' else 24
     gen.play(net, plies, hidden)
     st = gen.stats()
@@ -84,3 +83,75 @@ def test_play_with_network_feeds_make_batch(game):
     tm, v = b['turn_mask'][live], b['value'][live]
     assert bool((v[tm == 0] == 0).all()) and float(v.abs().max()) <= 1.0
     assert float(v[tm == 1].abs().sum()) > 0
+
+
+def test_recorded_logits_are_what_the_learner_recomputes():
+    """the behaviour logits/values recorded by `play` must come from the same per-player
+    recurrent context that `forward_prediction` (train.py:160-175) rebuilds from the batch: windows that start at
+    ply 0 of an episode, zero (B, P) hidden state, same weights -> the recomputed masked policy and the values
+    equal the recorded ones (up to cuDNN's batch-shape dependent summation order)."""
+    from handyrl_b200 import nets
+    from handyrl_b200.generation import BatchGenerator
+    from handyrl_b200.learner import forward_prediction
+    from handyrl_b200.train import make_batch_windows
+    N, T = 96, 12
+    torch.manual_seed(3)
+    net = nets.GeisterNet().cuda().eval()
+    gen = BatchGenerator('Geister', N, seed=21, depth=64, record_values=True, record_logits=True)
+    gen.play(net, T, gen.init_hidden(net))
+    # windows = plies 0..T-1 of every slot's first episode (no game ends within 12 plies)
+    win = torch.zeros(N, 8, dtype=torch.int32, device='cuda')
+    win[:, 0] = torch.arange(N)
+    win[:, 3], win[:, 5], win[:, 6] = T, 200, 3
+    args = dict(ARGS, forward_steps=T)
+    b = make_batch_windows(gen.store, win, args)
+    assert float(b['episode_mask'].min()) == 1.0
+    h0 = tuple([t.cuda() for t in part] for part in net.init_hidden([N, 2]))
+    with torch.no_grad():
+        out = forward_prediction(net, h0, b, args)
+    legal = b['action_mask'] == 0
+    assert bool((b['policy'][~legal] == -1e32).all())
+    d = (out['policy'] - b['policy'])[legal].abs().max().item()
+    assert d < 2e-4, d
+    tm = b['turn_mask'] > 0
+    dv = (out['value'] - b['value'])[tm].abs().max().item()
+    assert dv < 2e-4, dv
+    # ... and it is NOT what a state shared by both players produces: at ply 2 (player 0's second observation, same
+    # board in both runs) the turn player's own state differs from "whatever the opponent just wrote"
+    gen2 = BatchGenerator('Geister', N, seed=21, depth=64, record_values=True, record_logits=True)
+    shared = tuple([t[:, 0].clone() for t in part] for part in gen.init_hidden(net))
+    for _ in range(T):
+        o = gen2.observe_turn()
+        r = net({'scalar': o['scalar'], 'board': o['main']}, shared)
+        shared = r['hidden']
+        gen2.act(r['policy'].float())
+    b2 = make_batch_windows(gen2.store, win, args)
+    same = (b2['policy'][:, :2] == b['policy'][:, :2]).all()
+    assert bool(same)            # the first ply of each player starts from zeros either way
+    assert bool((b2['action_mask'][:, 2] == b['action_mask'][:, 2]).all())
+    assert (b2['policy'][:, 2] - b['policy'][:, 2])[legal[:, 2]].abs().max() > 1e-4
+
+
+def test_parallel_tictactoe_records_both_players_logits():
+    """SOLO windows of player 1 must carry player 1's behaviour logits."""
+    from handyrl_b200.generation import BatchGenerator
+    from handyrl_b200.train import make_batch_windows
+    N, T = 128, 4
+    gen = BatchGenerator('ParallelTicTacToe', N, seed=2, depth=16, record_values=True, record_logits=True)
+    g = torch.Generator(device='cuda').manual_seed(1)
+    fed = []
+    for _ in range(T):
+        gen.observe_turn()
+        lg = torch.randn(N, 2, 9, device='cuda', generator=g)
+        fed.append(lg)
+        gen.act(lg, values=torch.rand(N, 2, device='cuda', generator=g))
+    fed = torch.stack(fed, 1)                                         # (N, T, 2, 9)
+    args = dict(ARGS, turn_based_training=False, forward_steps=T)
+    for solo in (0, 1):
+        win = torch.zeros(N, 8, dtype=torch.int32, device='cuda')
+        win[:, 0] = torch.arange(N)
+        win[:, 3], win[:, 5], win[:, 6], win[:, 7] = 3, 9, 3, solo    # 3 plies: no game can end before its 5th ply... of one colour
+        b = make_batch_windows(gen.store, win, args)
+        legal = b['action_mask'][:, :3, 0] == 0
+        assert bool((b['policy'][:, :3, 0][legal] == fed[:, :3, solo][legal]).all())
+        assert bool((b['policy'][:, :3, 0][~legal] == -1e32).all())

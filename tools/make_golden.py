@@ -107,7 +107,7 @@ def _play_tapes(env_module, n_games, parallel, seed0):
 def gen_games():
     import importlib
     for name, n_games, parallel in (('tictactoe', 200, False), ('parallel_tictactoe', 200, True),
-                                    ('geister', 48, False), ('ci_geister', 16, False)):
+                                    ('geister', 256, False), ('ci_geister', 64, False)):
         mod = importlib.import_module('handyrl.envs.' + name)
         out = _play_tapes(mod, n_games, parallel, seed0=1000)
         np.savez_compressed(os.path.join(GOLD, "tape_%s.npz" % name), **out)
@@ -188,6 +188,101 @@ def gen_batch():
     with open(os.path.join(GOLD, "batch_cases.pkl"), "wb") as f:
         pickle.dump(cases, f, protocol=4)
     print("batch_cases.pkl:", os.path.getsize(os.path.join(GOLD, "batch_cases.pkl")), "bytes")
+
+
+NET_BATCH_CASES = [
+    # name, env module, B, T, compress_steps, turn_based_training, observation, episodes
+    ('ttt_net_turn', 'tictactoe', 10, 4, 4, True, False, 8),
+    ('ttt_net_all', 'tictactoe', 8, 5, 2, True, True, 6),
+    ('pttt_net_solo', 'parallel_tictactoe', 12, 5, 4, False, False, 8),
+    ('geister_net_turn', 'geister', 6, 16, 4, True, False, 3),
+    ('geister_net_all', 'geister', 4, 8, 4, True, True, 2),
+]
+
+
+def gen_netbatch():
+    """Batches of episodes generated WITH A NETWORK in the loop (handyrl/generation.py:36-57 records the net's
+    value and masked policy per moment; handyrl/train.py:60-82 copies them into the batch): the reference's
+    Generator + make_batch with a seeded reference net.  The fixture keeps the action tape and the per-ply net
+    outputs, so the device ring can be filled with exactly these numbers and b200rl_make_batch compared bit for bit
+    on `policy` and `value` (and everything else)."""
+    import bz2
+    import importlib
+    import pickle
+    import random
+    import torch
+    from handyrl.generation import Generator
+    from handyrl.model import ModelWrapper
+    from handyrl.train import make_batch
+    from handyrl_b200.train import select_episode
+
+    cases = {}
+    for ci, (name, envname, B, T, cs, tbt, obs, n_ep) in enumerate(NET_BATCH_CASES):
+        mod = importlib.import_module('handyrl.envs.' + envname)
+        env = mod.Environment()
+        A = env.action_length()
+        args = {'turn_based_training': tbt, 'observation': obs, 'gamma': 0.8, 'forward_steps': T,
+                'compress_steps': cs, 'maximum_episodes': 1000}
+        gen = Generator(env, args)
+        torch.manual_seed(4000 + ci)
+        net = env.net()()
+        net.eval()
+        models = {p: ModelWrapper(net) for p in env.players()}
+        random.seed(600 + ci)
+        episodes, tapes = [], []
+        parallel = envname == 'parallel_tictactoe'
+        for _ in range(n_ep):
+            ep = gen.generate(models, {})
+            moments = sum([pickle.loads(bz2.decompress(ms)) for ms in ep['moment']], [])
+            PL = 2 if parallel else 1
+            values = np.zeros((len(moments), 2), np.float32)
+            logits = np.zeros((len(moments), PL, A), np.float32)
+            for k, m in enumerate(moments):
+                for p in (0, 1):
+                    if m['value'][p] is not None:
+                        values[k, p] = np.asarray(m['value'][p], np.float32).reshape(-1)[0]
+                    if m['policy'][p] is not None:
+                        legal = m['action_mask'][p] == 0
+                        assert m['policy'][p].dtype == np.float32
+                        logits[k, p if parallel else 0][legal] = m['policy'][p][legal]   # raw logits where legal
+            if parallel:
+                acts = [[m['action'][0], m['action'][1]] for m in moments]
+                sel = [0 if color == env.BLACK else 1 for color, _ in env.record]
+                landed = [a for _, a in env.record]
+            else:
+                landed = [m['action'][m['turn'][0]] for m in moments]
+                acts = [[a, a] for a in landed]
+                sel = [0] * len(landed)
+            tapes.append({'actions': np.asarray(landed, np.int32), 'both': np.asarray(acts, np.int32),
+                          'sel': np.asarray(sel, np.int32), 'steps': ep['steps'],
+                          'outcome': [ep['outcome'][0], ep['outcome'][1]], 'values': values, 'logits': logits})
+            episodes.append(ep)
+        rng = random.Random(950 + ci)
+        picks = []
+        for _ in range(B):
+            w = select_episode(episodes, args, rng)
+            idx = [i for i, e in enumerate(episodes) if e['outcome'] is w['outcome'] and e['steps'] == w['total']
+                   and e['moment'][w['base'] // cs:][:len(w['moment'])] == w['moment']][0]
+            picks.append((idx, w))
+        random.seed(88 + ci)
+        out = make_batch([w for _, w in picks], args)
+        flat = {}
+        for k, v in out.items():
+            if isinstance(v, dict):
+                for kk, vv in v.items():
+                    flat['observation.' + kk] = vv.numpy()
+            else:
+                flat[k] = v.numpy()
+        cases[name] = {'env': envname, 'args': args, 'tapes': tapes,
+                       'windows': [(idx, w['start'], w['end'], w['total']) for idx, w in picks],
+                       'ep_minimum': [w for _, w in picks], 'seed': 88 + ci, 'out': flat}
+        nz = float(np.abs(flat['value']).sum())
+        print(name, {k: v.shape for k, v in flat.items() if k in ('policy', 'value')}, 'sum|value| %.3f' % nz)
+        assert nz > 0
+    blob = bz2.compress(pickle.dumps(cases, protocol=4))
+    with open(os.path.join(GOLD, "net_batch_cases.pkl.bz2"), "wb") as f:
+        f.write(blob)
+    print("net_batch_cases.pkl.bz2:", len(blob), "bytes")
 
 
 LOSS_CASES = [
