@@ -137,7 +137,8 @@ def cpu_hotpath_runner(seed):
     targets for both heads.  Returns (runner, cores) with the replay lists pre-filled (untimed)."""
     from oracle import games_c
     cores = os.cpu_count() or 1
-    hp = games_c.HotPath(CPU_GAMES_PER_THREAD, PLIES, T, cores, replay_cap=1024, seed=seed)
+    hp = games_c.HotPath(CPU_GAMES_PER_THREAD, PLIES, T, cores, replay_cap=1024, seed=seed,
+                         gamma=TRAIN_ARGS['gamma'], lmb=TRAIN_ARGS['lambda'])
     for _ in range(8):      # Geister games last ~157 plies: let every thread finish episodes before timing
         hp.step()
     return hp, cores
@@ -165,6 +166,20 @@ def cpu_baseline(seconds_target=12.0):
     return {"value": n / dt, "unit": "env-steps/s", "cores": cores, "kind": "port",
             "sample": cpu_sample_text(cores, steps, dt),
             "phase_share": {"generation": ph[0] / tot, "make_batch": ph[1] / tot, "targets": ph[2] / tot}}
+
+
+def cpu_baseline_reference(seconds=6.0):
+    """The UNMODIFIED reference's own Python path (baseline/_ref, installed by tools/install_ref.sh) timed on this
+    box's host cores in os.cpu_count() single-threaded processes: Generator.generate (RandomModel and GeisterNet),
+    make_batch, losses.compute_target - a separate process so that its torch thread settings and
+    forks stay away from this one."""
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "time_reference.py"), "--seconds", str(seconds),
+                            "--parts", "generation,generation_net,make_batch,targets"], stdout=subprocess.PIPE,
+                           stderr=subprocess.PIPE, timeout=300, text=True)
+        return json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception as ex:       # reported, never fatal for the GPU numbers
+        return {"unavailable": "time_reference.py failed: %r" % (ex,)}
 
 
 RESULT_OUT = sys.stdout
@@ -296,17 +311,30 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    phase_evs = [[ev() for _ in range(4)] for _ in range(args.steps)]
+    # The K timed steps are repeated in `rounds` back-to-back rounds so that the timed region lasts >= 0.35 s (20
+    # steps are only 33 ms: one or two nvidia-smi samples); every number below is the mean over K * rounds steps.
+    t_probe0, t_probe1 = ev(), ev()
+    t_probe0.record()
+    step(0)
+    t_probe1.record()
+    torch.cuda.synchronize()
+    rounds = max(1, int(0.35 / (args.steps * t_probe0.elapsed_time(t_probe1) * 1e-3) + 0.999))
+    if world > 1:
+        rr = torch.tensor([rounds], device=dev)
+        dist.all_reduce(rr, op=dist.ReduceOp.MAX)
+        rounds = int(rr.item())
+    n_timed = args.steps * rounds
+    phase_evs = [[ev() for _ in range(4)] for _ in range(n_timed)]
     e0, e1 = ev(), ev()
     barrier()
     e0.record()
-    for k in range(args.steps):
+    for k in range(n_timed):
         step(k, phase_evs[k])
     e1.record()
     barrier()
     total_ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
-    ph = [sum(p[i].elapsed_time(p[i + 1]) for p in phase_evs) / args.steps for i in range(3)]
+    ph = [sum(p[i].elapsed_time(p[i + 1]) for p in phase_evs) / n_timed for i in range(3)]
     if world > 1:
         tt = torch.tensor([total_ms] + ph, device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -314,25 +342,59 @@ def main():
     roll_ms, batch_ms, tgt_ms = ph
 
     env_steps_per_step = N_GAMES * PLIES * world
-    value = env_steps_per_step * args.steps / (total_ms * 1e-3)
+    value = env_steps_per_step * n_timed / (total_ms * 1e-3)
 
     # ---------------- e2e: the same step through the public API with the replay index on the host ----------
     e2e = None
     if not args.no_e2e:
-        # Software-pipelined like the reference's asynchronous batchers: while the GPU runs rollout k and the
-        # batch/targets of the windows chosen from rollouts <= k-2, the host draws the next windows from the rows of
-        # rollouts <= k-1 and then takes in the finished-episode rows of rollout k.
+        # Software-pipelined like the reference's asynchronous batchers (train.py:261-309: selection and batch
+        # making run beside the trainer).  The calling thread only ENQUEUES: rollout k, the D2H of its new episode
+        # rows, the H2D of the windows of step k (drawn two steps earlier), make_batch, targets, the D2H of the
+        # summary; it reads the summary of step k-2, which has long landed.  A background thread owns the replay
+        # index: it waits for the rows of rollout k, commits them and draws the windows of step k+2
+        # (b200rl_select_windows_host through ctypes: the GIL is released).  Nothing on the calling thread waits for
+        # the GPU or for the selection unless the GPU queue is two steps deep, i.e. the run is GPU-bound.
+        import queue
+        import threading
         st = gen.store
         torch.cuda.synchronize()
-        index = HostReplayIndex(gen, max_new_rows=1 << 15, n_threads=max(1, min(8, (os.cpu_count() or 1) // world)))
-        win_pin = [torch.empty(B, 8, dtype=torch.int32).pin_memory() for _ in range(2)]
-        win_devs = [torch.empty(B, 8, dtype=torch.int32, device=dev) for _ in range(2)]
+        # slab of 65,536 rows per read-back: a rollout finishes ~13,400 episodes and commits lag up to two steps
+        index = HostReplayIndex(gen, max_new_rows=1 << 16, n_threads=max(1, min(8, (os.cpu_count() or 1) // world - 1)),
+                                slots=4)
+        DEPTH = 3                                            # window / summary slots in flight
+        LOOK = 2                                             # windows of step k are drawn after rollout k-2
+        win_pin = [torch.empty(B, 8, dtype=torch.int32).pin_memory() for _ in range(DEPTH)]
+        win_devs = [torch.empty(B, 8, dtype=torch.int32, device=dev) for _ in range(DEPTH)]
+        met_pin = [torch.zeros(4, dtype=torch.float32).pin_memory() for _ in range(DEPTH)]
         copy_stream = torch.cuda.Stream(device=dev)      # PCIe traffic runs beside the kernels, ordered by events
-        ev_roll = torch.cuda.Event()
-        ev_h2d = [torch.cuda.Event() for _ in range(2)]
-        met_pin = torch.zeros(4, dtype=torch.float32).pin_memory()
-        ev_done = torch.cuda.Event()
-        hs = {"win": None, "h2d": None, "slot": 0, "pending": False, "metric": 0.0, "d2h": 0}
+        ev_roll = [torch.cuda.Event() for _ in range(DEPTH)]
+        ev_h2d = [torch.cuda.Event() for _ in range(DEPTH)]
+        ev_done = [torch.cuda.Event() for _ in range(DEPTH)]
+        win_ready = [threading.Event() for _ in range(DEPTH)]
+        jobs = queue.Queue()
+        hs = {"metric": 0.0, "d2h": 0, "select_s": 0.0, "select_n": 0, "err": None}
+
+        def selector():
+            """background: rows of rollout j -> commit -> windows of step j + LOOK"""
+            try:
+                torch.cuda.set_device(dev)
+                while True:
+                    job = jobs.get()
+                    if job is None:
+                        return
+                    j, it_after, ticket = job
+                    index.commit(ticket)                                         # waits: rows of rollout j have landed
+                    t_s = pc()
+                    slot = (j + LOOK) % DEPTH
+                    index.select(B, TRAIN_ARGS, win_pin[slot], seed=rank, lookahead=LOOK * PLIES, it_now=it_after)
+                    hs["select_s"] += pc() - t_s
+                    hs["select_n"] += 1
+                    hs["d2h"] = index.d2h_bytes
+                    win_ready[slot].set()
+            except Exception as ex:                                              # surface in the main thread
+                hs["err"] = ex
+                for w_ in win_ready:
+                    w_.set()
 
         def step_tail(k, win):
             state["batch"] = batch = make_batch_windows(gen.store, win, TRAIN_ARGS, out=state["batch"])
@@ -342,84 +404,95 @@ def main():
             return t1, t2
 
         e2e_evs = []
-        tr_acc = {"enqueue_rollout": 0.0, "wait_prev_result": 0.0, "enqueue_tail": 0.0, "wait_fetch": 0.0,
-                  "host_select": 0.0}
+        tr_acc = {"enqueue_rollout_fetch": 0.0, "wait_windows": 0.0, "enqueue_tail": 0.0, "wait_result_2_steps_late": 0.0}
         pc = time.perf_counter
 
         def e2e_step(k):
+            """k counts from 0 over warm-up + timed steps; steps 0..LOOK-1 have no windows yet (rollout only)"""
             t_a = pc()
+            s = k % DEPTH
             evk = [ev() for _ in range(6)]
             e2e_evs.append(evk)
             evk[0].record()
             gen.rollout(PLIES, waves=waves, out_action=act_w)                   # async
             evk[1].record()
-            ev_roll.record()
+            ev_roll[s].record()
             with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(ev_roll)
-                index.fetch_async()                                             # D2H: counters + new episode rows
+                copy_stream.wait_event(ev_roll[s])
+                ticket = index.fetch_async()                                    # D2H: counters + new episode rows
             evk[2].record()
+            win_ready[(k + LOOK) % DEPTH].clear()
+            jobs.put((k, gen.store.it, ticket))
             t_b = pc()
-            if hs["pending"]:                                                   # D2H result of the previous step
-                ev_done.synchronize()
-                hs["metric"] = float(met_pin[0])
-                hs["pending"] = False
-            t_c = pc()
-            if hs["win"] is not None:
-                torch.cuda.current_stream().wait_event(hs["h2d"])               # H2D of these windows (copy stream)
+            t_c = t_b
+            if k >= LOOK:
+                win_ready[s].wait()                                             # drawn two steps ago: normally set
+                if hs["err"] is not None:
+                    raise hs["err"]
+                t_c = pc()
+                with torch.cuda.stream(copy_stream):                            # H2D of this step's windows
+                    win_devs[s].copy_(win_pin[s], non_blocking=True)
+                    ev_h2d[s].record()
+                torch.cuda.current_stream().wait_event(ev_h2d[s])
                 evk[3].record()
-                (tv, av), (tr, ar) = step_tail(k, hs["win"])
+                (tv, av), (tr, ar) = step_tail(k, win_devs[s])
                 evk[4].record()
-                met_pin.copy_(torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()]), non_blocking=True)
+                met_pin[s].copy_(torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()]), non_blocking=True)
                 evk[5].record()
-                ev_done.record()
-                hs["pending"] = True
+                ev_done[s].record()
             t_d = pc()
-            # ---- host work, overlapped with the GPU: draw the next windows from the episodes indexed so far (the
-            # rows of rollouts <= k-1), THEN take in the rows of rollout k, whose read-back has landed by then ----
-            slot = hs["slot"]
-            hs["slot"] ^= 1
-            buf = index.select(B, TRAIN_ARGS, win_pin[slot], seed=rank, lookahead=PLIES)
-            with torch.cuda.stream(copy_stream):                                # H2D: windows for the next step
-                win_devs[slot].copy_(buf, non_blocking=True)
-                ev_h2d[slot].record()
-            hs["win"], hs["h2d"] = win_devs[slot], ev_h2d[slot]
+            if k >= 2 * LOOK:                                                   # result of step k-2 (D2H landed long ago)
+                ev_done[(k - LOOK) % DEPTH].synchronize()
+                hs["metric"] = float(met_pin[(k - LOOK) % DEPTH][0])
             t_e = pc()
-            index.commit()
-            hs["d2h"] = index.d2h_bytes
-            t_f = pc()
-            for name, dt_ in zip(tr_acc, (t_b - t_a, t_c - t_b, t_d - t_c, t_f - t_e, t_e - t_d)):
+            for name, dt_ in zip(tr_acc, (t_b - t_a, t_c - t_b, t_d - t_c, t_e - t_d)):
                 tr_acc[name] += dt_
 
-        for k in range(4):
+        th = threading.Thread(target=selector, daemon=True)
+        th.start()
+        n_warm = 6
+        for k in range(n_warm):
             e2e_step(k)
         barrier()
         ksteps = max(5, min(args.steps, 20))
+        e2e_rounds = max(1, int(0.35 / (ksteps * total_ms / (args.steps * rounds) * 1e-3) + 0.999))
         for name in tr_acc:
             tr_acc[name] = 0.0
+        hs["select_s"], hs["select_n"] = 0.0, 0
         e2e_evs.clear()
         t0 = time.perf_counter()
-        for k in range(ksteps):
-            e2e_step(k)
-        if hs["pending"]:
-            ev_done.synchronize()
+        for k in range(ksteps * e2e_rounds):
+            e2e_step(n_warm + k)
+        last = n_warm + ksteps * e2e_rounds - 1
+        for k in (last - 1, last):                                              # drain the two results still in flight
+            ev_done[k % DEPTH].synchronize()
+            hs["metric"] = float(met_pin[k % DEPTH][0])
         barrier()
         dt = time.perf_counter() - t0
+        jobs.put(None)
+        th.join(timeout=10)
+        n_e2e = ksteps * e2e_rounds
         if world > 1:
             tt = torch.tensor([dt], device=dev, dtype=torch.float64)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt.item())
-        e2e = {"value": N_GAMES * PLIES * ksteps * world / dt, "unit": "env-steps/s",
+        timed_evs = [e_ for e_ in e2e_evs if True]
+        e2e = {"value": N_GAMES * PLIES * n_e2e * world / dt, "unit": "env-steps/s",
                "h2d_bytes_per_step": int(win_devs[0].numel() * 4),
-               "d2h_bytes_per_step": int(hs["d2h"] + met_pin.numel() * 4),
-               "steps": ksteps, "ms_per_step": dt / ksteps * 1e3,
-               "host_ms_per_step": {name: round(v_ / ksteps * 1e3, 4) for name, v_ in tr_acc.items()},
-               "gpu_ms_per_step": {name: round(sum(e_[i].elapsed_time(e_[i + 1]) for e_ in e2e_evs) / len(e2e_evs), 4)
+               "d2h_bytes_per_step": int(hs["d2h"] + met_pin[0].numel() * 4),
+               "steps": n_e2e, "ms_per_step": dt / n_e2e * 1e3,
+               "host_ms_per_step": {name: round(v_ / n_e2e * 1e3, 4) for name, v_ in tr_acc.items()},
+               "selector_thread_ms_per_step": round(hs["select_s"] / max(hs["select_n"], 1) * 1e3, 4),
+               "selector_threads": index.n_threads,
+               "gpu_ms_per_step": {name: round(sum(e_[i].elapsed_time(e_[i + 1]) for e_ in timed_evs) / len(timed_evs), 4)
                                    for i, name in enumerate(("rollout", "enqueue_gap", "wait_h2d_windows",
                                                              "make_batch_targets", "summary_d2h"))},
-               "note": "per step: BatchGenerator.rollout; D2H of the counters and the new finished-episode rows; "
-                       "HostReplayIndex.select (b200rl_select_windows_host, replay index on the host) overlapped with the GPU; pinned H2D of the "
-                       "windows on a copy stream (event-ordered) beside the kernels; make_batch_windows; compute_target_heads (value + return head, one launch); D2H of the target summary. Moments stay in "
-                       "HBM (the trajectory ring is the replay buffer). Wall clock incl. all host work."}
+               "note": "per step, calling thread (enqueue only): BatchGenerator.rollout; D2H of the counters and the "
+                       "new finished-episode rows; pinned H2D of the windows drawn two steps earlier (copy stream, "
+                       "event-ordered); make_batch_windows; compute_target_heads (value + return head, one launch); D2H "
+                       "of the target summary, read two steps late.  Background thread: HostReplayIndex.commit + "
+                       "select (b200rl_select_windows_host, replay index on the host).  Moments stay in HBM (the "
+                       "trajectory ring is the replay buffer).  Wall clock incl. all host work."}
 
         # the same self-play driven ply by ply from HOST buffers (reference Environment-style stepping: actions
         # H2D, observation / legal bits / reward / terminal D2H every ply) — PCIe-bound by the fp32 observations
@@ -491,7 +564,8 @@ def main():
                 roofs[k]["traffic"] = tr.get(k)
         line = {
             "metric": "geister_selfplay_env_steps_per_sec", "value": value, "unit": "env-steps/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / n_timed,
+            "rounds": rounds, "timed_steps": n_timed, "timed_region_ms": total_ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64 bitboards -> f32", "data": "synthetic", "config": workload_config(world),
             "target_timesteps_per_sec": B * T * P * world / (tgt_ms * 1e-3),
@@ -499,10 +573,11 @@ def main():
             "phases": {"rollout_ms": roll_ms, "make_batch_ms": batch_ms, "targets_ms": tgt_ms,
                        "env_steps_per_sec_rollout_only": env_steps_per_step / (roll_ms * 1e-3)},
             "roofline": roofs[dominant], "rooflines": roofs,
-            "clocks": clocks, "e2e": e2e, "gpu_launches": 4 * args.steps,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": 4 * n_timed,
         }
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline()
+            line["cpu_baseline_reference"] = cpu_baseline_reference()
         print(json.dumps(line), file=RESULT_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -65,7 +65,9 @@ SIGNATURES = {
     "b200rl_env_info": [c_int, c_ptr, c_i64, c_ptr, c_ptr],
     "b200rl_env_step_observe": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_int] + [c_ptr] * 8,
     "b200rl_env_rollout": [c_int, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
-                           c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr],
+                           c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr],
+    "b200rl_env_rollout_scratch_bytes": [c_i64],
+    "b200rl_set_tuning": [ctypes.c_char_p, c_i64, c_int],
     "b200rl_env_step_record": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_int, c_ptr, c_i64, c_u64, c_ptr, c_i64,
                                c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "b200rl_env_logit_slots": [c_int],
@@ -82,7 +84,8 @@ SIGNATURES = {
 }
 
 # functions that return a value instead of a status
-_RESTYPE = {"b200rl_env_state_bytes": c_i64, "b200rl_env_logit_slots": c_i64}
+_RESTYPE = {"b200rl_env_state_bytes": c_i64, "b200rl_env_logit_slots": c_i64,
+            "b200rl_env_rollout_scratch_bytes": c_i64}
 
 
 def lib():
@@ -114,6 +117,11 @@ def check(status, what=""):
 
 def call(name, *args):
     check(getattr(lib(), name)(*args), name)
+
+
+def set_tuning(name, value=None):
+    """Set (or, with value=None, clear) a tuning knob of the library (include/b200rl.h: b200rl_set_tuning)."""
+    call("b200rl_set_tuning", name.encode(), 0 if value is None else int(value), 0 if value is None else 1)
 
 
 def stream_ptr():

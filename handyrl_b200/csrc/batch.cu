@@ -513,6 +513,9 @@ __host__ __device__ inline void select_one_window(const int32_t* ep_table, int64
         const double accept = 1.0 - (double)(L - 1 - ep_idx) / (double)maximum_episodes;         // train.py:287
         const bool last_try = tr == 63;
         if (last_try) ep_idx = L - 1;
+        // train.py:288 first: a try rejected by the recency law never needs its table row (one random 16-byte
+        // read less per rejection; the outcome is the same as testing `alive && accepted`)
+        if (!last_try && !((double)r1 * (1.0 / 4294967296.0) < accept)) continue;
         const unsigned long long pos = cursor - (unsigned long long)L + (unsigned long long)ep_idx;
         const int32_t* e = ep_table + (int64_t)(e_pow2 ? (pos & (unsigned long long)(E - 1)) : (pos % (unsigned long long)E)) * 4;
         slot = e[0];
@@ -520,7 +523,7 @@ __host__ __device__ inline void select_one_window(const int32_t* ep_table, int64
         win = (e[1] >> 16) & 3;
         end_it = (uint64_t)(uint32_t)e[2] | ((uint64_t)(uint32_t)e[3] << 32);
         const bool alive = it_now - (end_it + 1 - (uint64_t)steps) <= (uint64_t)D;
-        if (last_try || (alive && (double)r1 * (1.0 / 4294967296.0) < accept)) break;  // train.py:288
+        if (last_try || alive) break;
     }
     // the window-start and solo-player draws of the accepted try (rejected tries never needed theirs)
     const uint32_t r2 = b200rl_rand32(seed, (uint64_t)b, c + 2), r3 = b200rl_rand32(seed, (uint64_t)b, c + 3);
@@ -723,17 +726,22 @@ extern "C" int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t 
                    "select_windows_host: bad E/D/maximum_episodes/forward_steps/B");
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 64) n_threads = 64;
-    // The table (16 B per finished episode, up to E rows) does not fit the host caches and every try of the
-    // rejection sampling reads one random row: the rows of the first two tries of the next PF windows are
-    // prefetched while the current block is drawn (the draws are counter-based, so they can be recomputed).
+    // The table (16 B per finished episode, up to E rows) does not fit the host caches and an accepted try reads
+    // one random row: that row is prefetched for the next PF windows while the current block is drawn (the draws
+    // are counter-based, so they can be recomputed).
     int64_t Lh = (int64_t)(cursor < (unsigned long long)E ? cursor : (unsigned long long)E);
     if (Lh > maximum_episodes) Lh = maximum_episodes;
-    auto prefetch = [&](int64_t b) {
+    auto prefetch = [&](int64_t b) {   // the row of the first try the recency law accepts (almost always the one used)
         if (Lh <= 0) return;
-        for (int tr = 0; tr < 2; ++tr) {
-            const uint32_t r0 = b200rl_rand32(seed, (uint64_t)b, draw0 + 4ull * (uint64_t)tr);
-            const unsigned long long pos = cursor - (unsigned long long)Lh + (((unsigned long long)r0 * (unsigned long long)Lh) >> 32);
+        for (int tr = 0; tr < 8; ++tr) {
+            const uint64_t c = draw0 + 4ull * (uint64_t)tr;
+            const uint32_t r0 = b200rl_rand32(seed, (uint64_t)b, c), r1 = b200rl_rand32(seed, (uint64_t)b, c + 1);
+            const int64_t ep_idx = (int64_t)(((unsigned long long)r0 * (unsigned long long)Lh) >> 32);
+            const double accept = 1.0 - (double)(Lh - 1 - ep_idx) / (double)maximum_episodes;
+            if (!((double)r1 * (1.0 / 4294967296.0) < accept)) continue;
+            const unsigned long long pos = cursor - (unsigned long long)Lh + (unsigned long long)ep_idx;
             __builtin_prefetch(ep_table_host + (int64_t)(pos % (unsigned long long)E) * 4);
+            return;
         }
     };
     constexpr int64_t PF = 16;

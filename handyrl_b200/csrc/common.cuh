@@ -13,6 +13,14 @@
 // Thread-local last-error message, read through b200rl_last_error().
 void b200rl_set_error(const char* fmt, ...);
 
+// tuning knobs (abi.cu): environment default read once, overridable through b200rl_set_tuning
+enum {
+    B200RL_TUNE_ROLLOUT_CHUNK = 0, B200RL_TUNE_TARGET_WS_STAGES, B200RL_TUNE_TARGET_WS_ROW,
+    B200RL_TUNE_TARGET_WS_WIDE_ROWS, B200RL_TUNE_TARGET_GENERIC, B200RL_TUNE_TARGET_NO_DUAL,
+    B200RL_TUNE_TARGET_PERSISTENT, B200RL_TUNE_COUNT
+};
+bool b200rl_tuning(int knob, long long* out);   // true when the knob is set (env or set_tuning)
+
 static inline int b200rl_check_launch(const char* what) {
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {

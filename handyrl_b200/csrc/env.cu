@@ -4,8 +4,8 @@
 // `Environment` interface (handyrl/environment.py:43-146) and the body of the
 // self-play loop that drives it (handyrl/generation.py:31-68).
 #include <cstdlib>
-#include <map>
-#include <mutex>
+
+#include <atomic>
 
 #include "common.cuh"
 #include "games.cuh"
@@ -509,39 +509,21 @@ inline int grid_for(int64_t N) { return (int)((N + BLK - 1) / BLK); }
 
 // persistent grid: as many CTAs as are resident at once (8 per SM for Geister at 128 registers, more for TicTacToe)
 template <class G>
-void launch_rollout(const RolloutParams& p, int64_t want, int sms, cudaStream_t stream) {
-    static int per_sm = 0;
+void launch_rollout(const RolloutParams& p, int64_t want, int dev, int sms, cudaStream_t stream) {
+    static std::atomic<int> per_sm_dev[64];   // per device: the occupancy query is a property of (kernel, device)
+    std::atomic<int>& slot = per_sm_dev[dev & 63];
+    int per_sm = slot.load(std::memory_order_relaxed);
     if (per_sm == 0) {
         int n = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_rollout<G>, BLK, 0) != cudaSuccess || n < 1) n = 8;
         per_sm = n;
+        slot.store(n, std::memory_order_relaxed);
     }
     const int grid = (int)min(want, (int64_t)sms * per_sm);
     k_rollout<G><<<grid, BLK, 0, stream>>>(p);
 }
 
 }  // namespace
-
-// Ticket scratch of the rollout, one buffer per (device, stream), grown on demand and kept for the process.
-static unsigned int* rollout_sched(int dev, void* stream, size_t words) {
-    static std::mutex mu;
-    static std::map<std::pair<int, void*>, std::pair<unsigned int*, size_t>> bufs;
-    std::lock_guard<std::mutex> lock(mu);
-    auto& e = bufs[std::make_pair(dev, stream)];
-    if (e.second < words) {
-        if (e.first) cudaFree(e.first);
-        e.first = nullptr;
-        e.second = 0;
-        const size_t cap = words + words / 2 + 1024;
-        if (cudaMalloc(&e.first, cap * sizeof(unsigned int)) != cudaSuccess) {
-            cudaGetLastError();
-            e.first = nullptr;
-            return nullptr;
-        }
-        e.second = cap;
-    }
-    return e.first;
-}
 
 #define DISPATCH_GAME(game, EXPR)                                                       \
     switch (game) {                                                                     \
@@ -644,12 +626,23 @@ extern "C" int b200rl_env_step_observe(int game, void* state, int64_t N, const i
     return b200rl_check_launch("k_step_observe");
 }
 
+// ticket scratch of one rollout launch: header + one progress word per group of 32 games
+extern "C" int64_t b200rl_env_rollout_scratch_bytes(int64_t N) {
+    if (N < 0) return -1;
+    return (int64_t)(SCHED_HDR + (N + 31) / 32) * (int64_t)sizeof(unsigned int);
+}
+
 extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_plies, uint64_t seed,
                                   uint64_t game_id_base, uint64_t it0, float* out_main, float* out_scalar,
                                   float* out_amask, int32_t* out_action, int64_t waves, void* traj, int64_t D,
-                                  int32_t* ep_table, int64_t E, uint64_t* counters, void* stream) {
+                                  int32_t* ep_table, int64_t E, uint64_t* counters, void* scratch,
+                                  int64_t scratch_bytes, void* stream) {
     REQ_STATE(state, N);
     B200RL_REQUIRE(n_plies >= 0, "env_rollout: negative n_plies");
+    B200RL_REQUIRE(scratch != nullptr && ((uintptr_t)scratch % 16) == 0 &&
+                       scratch_bytes >= b200rl_env_rollout_scratch_bytes(N),
+                   "env_rollout: the caller-owned ticket scratch must hold b200rl_env_rollout_scratch_bytes(N) bytes, "
+                   "16-byte aligned");
     B200RL_REQUIRE(aligned16(out_main) && aligned16(out_scalar) && aligned16(out_amask) && ((uintptr_t)traj % 32) == 0,
                    "env_rollout: outputs must be 16-byte aligned (trajectory ring: 32)");
     B200RL_REQUIRE(!(out_main || out_scalar || out_amask || out_action) || waves >= 1, "env_rollout: waves must be >= 1");
@@ -669,10 +662,10 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int64_t ngroups = (N + 31) / 32;
-    static const char* chunk_env = getenv("B200RL_ROLLOUT_CHUNK");   // experiments: 0 = one chunk per group (static)
+    long long chunk_knob = 0;   // knob rollout_chunk (experiments): 0 = one chunk per group (static schedule)
     int64_t chunk;
-    if (chunk_env) {
-        chunk = atoll(chunk_env);
+    if (b200rl_tuning(B200RL_TUNE_ROLLOUT_CHUNK, &chunk_knob)) {
+        chunk = chunk_knob;
     } else {
         // a ticket should move ~256 KB (Geister with full moments: 4 plies x 32 games x 1972 B) so that the ticket
         // overhead (atomic, 64 B/game state round trip, fence) stays ~1 %; always a multiple of the 4-ply record line
@@ -687,12 +680,11 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     if (chunk <= 0 || n_plies < 2 * chunk || ngroups < 2 * sms) chunk = n_plies;
     const int64_t nchunks = (n_plies + chunk - 1) / chunk;
     B200RL_REQUIRE(ngroups * nchunks < (int64_t)0xFFFF0000u, "env_rollout: too many tickets (N * n_plies)");
-    unsigned int* sched = rollout_sched(dev, stream, (size_t)(SCHED_HDR + ngroups));
-    B200RL_REQUIRE(sched != nullptr, "env_rollout: cannot allocate the ticket scratch (first call inside a graph capture?)");
+    unsigned int* sched = (unsigned int*)scratch;
     cudaMemsetAsync(sched, 0, (size_t)(SCHED_HDR + ngroups) * sizeof(unsigned int), (cudaStream_t)stream);
     p.sched = sched;
     p.chunk = chunk;
     const int64_t want = (ngroups + WARPS - 1) / WARPS;
-    DISPATCH_GAME(game, launch_rollout<G>(p, want, sms, (cudaStream_t)stream));
+    DISPATCH_GAME(game, launch_rollout<G>(p, want, dev, sms, (cudaStream_t)stream));
     return b200rl_check_launch("k_rollout");
 }

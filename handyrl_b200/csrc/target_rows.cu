@@ -627,7 +627,7 @@ int launch_shape(const ScanParams& k, cudaStream_t st) {
     // HBM bandwidth they can draw (tools/probe_write4.cu), so a static tile stride runs at the pace of the slowest
     // SM (6.3 TB/s for a pure write stream) while dynamic dispatch reaches 7.3.  B200RL_TARGET_PERSISTENT=1
     // restores the persistent grid-stride launch for A/B measurements.
-    static const bool persistent = getenv("B200RL_TARGET_PERSISTENT") != nullptr;
+    const bool persistent = b200rl_tuning(B200RL_TUNE_TARGET_PERSISTENT, nullptr);
     const int grid = persistent ? min(ntiles, sms * per_sm) : ntiles;
     kern<<<grid, 32, SMEM, st>>>(k, ntiles, alias ? 1 : 0, ns);
     return b200rl_check_launch("k_target_rows");
@@ -681,8 +681,8 @@ int launch_ws(const ScanParams& k, cudaStream_t st) {
     });
     const int ntiles = (k.B + TR - 1) / TR;
     const int want = (ntiles + sms - 1) / sms;   // CTAs an SM holds when the whole grid is resident
-    const char* ns_e = getenv("B200RL_TARGET_WS_STAGES");
-    const int ns_env = ns_e ? atoi(ns_e) : 0;
+    long long ns_knob = 0;
+    const int ns_env = b200rl_tuning(B200RL_TUNE_TARGET_WS_STAGES, &ns_knob) ? (int)ns_knob : 0;
     int ns = 2;
     while (ns < WS_MAX_STAGES && (size_t)want * (BAR + (ns + 1) * stage + 1024) <= (size_t)220 * 1024) ++ns;
     if (ns_env >= 2 && ns_env <= WS_MAX_STAGES) ns = ns_env;
@@ -694,12 +694,12 @@ int launch_ws(const ScanParams& k, cudaStream_t st) {
 // Chunk width of the warp-specialised kernel: 256 B per row and fetch up to B200RL_TARGET_WS_WIDE_ROWS batch rows
 // (more chunks in flight per CTA while few CTAs share an SM), 512 B beyond (measured at B = 65,536: +3-9 % at
 // T = 200, +2-4 % at T = 1024; at B = 16,384 and T = 200 the wide chunks are 15 % slower).
-// B200RL_TARGET_WS_ROW=256 / 512 forces either (read at every call, so that a test can cover both in one process).
+// Knob target_ws_row = 256 / 512 forces either (b200rl_set_tuning, so that a test can cover both in one process).
 inline int ws_row_bytes(int B) {
-    const char* e = getenv("B200RL_TARGET_WS_ROW");
-    if (e) return atoi(e) >= 512 ? 512 : 256;
-    const char* w = getenv("B200RL_TARGET_WS_WIDE_ROWS");
-    return B >= (w ? atoi(w) : 32768) ? 512 : 256;
+    long long v = 0;
+    if (b200rl_tuning(B200RL_TUNE_TARGET_WS_ROW, &v)) return v >= 512 ? 512 : 256;
+    const long long wide = b200rl_tuning(B200RL_TUNE_TARGET_WS_WIDE_ROWS, &v) ? v : 32768;
+    return B >= wide ? 512 : 256;
 }
 
 // long rows: the warp-specialised kernel (16-row tiles at P = 2); rows of <= 64 steps: one warp per 32 x 16 tile

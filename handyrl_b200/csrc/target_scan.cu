@@ -302,7 +302,7 @@ ScanParams make_params(const float* values, int64_t v_sb, int64_t v_st, int64_t 
 
 int launch_one(int mode_targets, int mode_adv, ScanParams& k, cudaStream_t stream) {
     // contiguous P<=2 layouts (what compute_loss produces): row-per-thread cp.async pipeline
-    static const bool force_generic = getenv("B200RL_TARGET_GENERIC") != nullptr;  // A/B switch for tools/sweep_targets.py
+    const bool force_generic = b200rl_tuning(B200RL_TUNE_TARGET_GENERIC, nullptr);  // A/B switch for tools/sweep_targets.py
     const bool has_rew = k.rew.p != nullptr;
     const int fast = force_generic ? -1 : b200rl_launch_target_rows(mode_targets, mode_adv, k, has_rew, stream);
     if (fast >= 0) return fast;
@@ -350,7 +350,7 @@ extern "C" int b200rl_target_scan_heads(int mode_targets, int mode_adv, const b2
                            x.out_adv, B, T, P, lmb, x.gamma);
     }
     if (B == 0) return B200RL_OK;
-    static const bool no_dual = getenv("B200RL_TARGET_GENERIC") != nullptr || getenv("B200RL_TARGET_NO_DUAL") != nullptr;
+    const bool no_dual = b200rl_tuning(B200RL_TUNE_TARGET_GENERIC, nullptr) || b200rl_tuning(B200RL_TUNE_TARGET_NO_DUAL, nullptr);
     if (n_heads == 2 && !no_dual) {
         const int rc = b200rl_launch_target_rows2(mode_targets, mode_adv, k[0], k[1], (cudaStream_t)stream);
         if (rc >= 0) return rc;

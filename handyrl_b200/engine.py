@@ -49,6 +49,9 @@ class BatchedEnv:
         self.obs_shape, self.scalar_shape = OBS_SHAPES[self.game]
         # SoA planes: [state_bytes/16][N] uint4 for Geister, [N] uint32 for TicTacToe
         self.state = torch.zeros(self.N * self.state_bytes // 4 + 4, dtype=torch.int32, device=self.device)
+        # ticket counters of rollout(): caller-owned, so the library allocates nothing behind the ABI
+        sb = int(lib.b200rl_env_rollout_scratch_bytes(self.N))
+        self._rollout_scratch = torch.zeros((sb + 3) // 4 + 4, dtype=torch.int32, device=self.device)
         self.it = 0  # global ply counter of rollout()
         self.reset()
 
@@ -172,7 +175,7 @@ class BatchedEnv:
             _lib.call("b200rl_env_rollout", self.game, self._st(), self.N, int(n_plies), int(seed),
                       int(game_id_base), int(self.it), _ptr(main), _ptr(scalar), _ptr(am), _ptr(out_action),
                       max(W, 1 if out_action is not None else 0), _ptr(traj), D, _ptr(ep_table), E, _ptr(counters),
-                      self._stream())
+                      _ptr(self._rollout_scratch), self._rollout_scratch.numel() * 4, self._stream())
         self.it += int(n_plies)
 
     # -- state access for the single-game facades and tests ------------------

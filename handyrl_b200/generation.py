@@ -66,56 +66,70 @@ class DeviceMoments:
 class HostReplayIndex:
     """Replay index on the host, like the reference Learner's `episodes` deque (train.py:480-503), for a
     device-resident trajectory store: a pinned mirror of the finished-episode table.  Only these 16-byte rows
-    cross PCIe; the moments stay in the trajectory ring.  `fetch_async` enqueues the read-back behind the
-    rollout on the current stream, `commit` waits for it, `select` draws windows with the SAME rule and RNG as
-    the device kernel (`b200rl_select_windows_host`) into a pinned buffer ready for upload.  `select` may run while
-    a `fetch_async` is in flight (it only reads rows below the committed cursor) as long as
-    `maximum_episodes + max_new_rows <= E`, i.e. the incoming rows do not wrap onto the ones being drawn from."""
+    cross PCIe; the moments stay in the trajectory ring.
 
-    def __init__(self, gen, max_new_rows=1 << 15, n_threads=4):
+    `fetch_async` enqueues the read-back of the counters and of a fixed slab of `max_new_rows` table rows starting
+    at the committed cursor, on the current stream, and returns a ticket; `commit(ticket)` waits for that copy and
+    advances the cursor; `select` draws windows with the SAME rule and RNG as the device kernel
+    (`b200rl_select_windows_host`) into a pinned buffer ready for upload.
+
+    Threading: `fetch_async` belongs to the thread that enqueues the rollouts, `commit` + `select` may run on a
+    background thread (both block without the GIL: event wait / ctypes call).  Several fetches may be in flight
+    (`slots`): each has its own pinned counter copy and event, and every slab starts at the cursor committed when it
+    was enqueued, so a lagging commit only makes slabs overlap (the same bytes are copied twice).  Rows beyond a
+    slab are picked up by the next fetch: the cursor never passes what has landed.  `select` only reads rows below
+    the committed cursor; keep `maximum_episodes + max_new_rows <= E` so that incoming rows do not wrap onto the
+    ones being drawn from."""
+
+    def __init__(self, gen, max_new_rows=1 << 15, n_threads=4, slots=4):
         st = gen.store
         self.gen, self.st = gen, st
         self.table = torch.zeros(st.E, 4, dtype=torch.int32).pin_memory()
-        self.ctr = torch.zeros(8, dtype=torch.int64).pin_memory()
-        self.event = torch.cuda.Event()
+        self.ctrs = [torch.zeros(8, dtype=torch.int64).pin_memory() for _ in range(slots)]
+        self.events = [torch.cuda.Event() for _ in range(slots)]
+        self._next_slot = 0
+        self._last_ticket = None
         self.max_new, self.n_threads = int(min(max_new_rows, st.E)), int(n_threads)
         self.table.copy_(st.ep_table)                          # one full read-back; later only the new rows
         self.cursor = self.read = int(st.counters[5].item())
         self.draws = 0
-        self.d2h_bytes = 0
-
-    def _copy_rows(self, a0, n, non_blocking):
-        E = self.st.E
-        n1 = min(n, E - a0)
-        self.table[a0:a0 + n1].copy_(self.st.ep_table[a0:a0 + n1], non_blocking=non_blocking)
-        if n1 < n:
-            self.table[:n - n1].copy_(self.st.ep_table[:n - n1], non_blocking=non_blocking)
-        self.d2h_bytes += n * 16
+        self.d2h_bytes = 64 + self.max_new * 16
 
     def fetch_async(self):
-        self.d2h_bytes = 64
-        self.ctr.copy_(self.st.counters, non_blocking=True)
-        self._copy_rows(self.read % self.st.E, self.max_new, True)
-        self.event.record()
+        slot = self._next_slot
+        self._next_slot = (slot + 1) % len(self.ctrs)
+        start = self.read                                      # committed cursor right now (a stale value is safe)
+        E, n = self.st.E, self.max_new
+        self.ctrs[slot].copy_(self.st.counters, non_blocking=True)
+        a0 = start % E
+        n1 = min(n, E - a0)
+        self.table[a0:a0 + n1].copy_(self.st.ep_table[a0:a0 + n1], non_blocking=True)
+        if n1 < n:
+            self.table[:n - n1].copy_(self.st.ep_table[:n - n1], non_blocking=True)
+        self.events[slot].record()
+        self._last_ticket = (slot, start)
+        return self._last_ticket
 
-    def commit(self):
-        self.event.synchronize()
-        cur = int(self.ctr[5])
-        if cur - self.read > self.max_new:          # more rows than the fixed slab: fetch the rest synchronously
-            lo = self.read + self.max_new
-            self._copy_rows(lo % self.st.E, min(cur - lo, self.st.E), False)
-        self.read = self.cursor = cur
-        return cur
+    def commit(self, ticket=None):
+        slot, start = ticket if ticket is not None else self._last_ticket
+        self.events[slot].synchronize()
+        cur = min(int(self.ctrs[slot][5]), start + self.max_new)    # rows past the slab wait for the next fetch
+        if cur > self.cursor:
+            self.read = self.cursor = cur
+        return self.cursor
 
-    def select(self, batch_size, args, out_pinned, seed=0, lookahead=0):
-        """`lookahead` = plies that will be generated between this call and the use of the windows (a pipelined
-        caller draws the windows of the next step while the current rollout runs): episodes whose first plies the
-        ring will have overwritten by then are skipped like rejected draws."""
+    def select(self, batch_size, args, out_pinned, seed=0, lookahead=0, it_now=None):
+        """`lookahead` = plies that will be generated between `it_now` (default: the store's current iteration) and
+        the use of the windows (a pipelined caller draws the windows of a later step while rollouts run): episodes
+        whose first plies the ring will have overwritten by then are skipped like rejected draws.  A caller that
+        selects on a background thread passes `it_now` explicitly (the store's counter belongs to the thread that
+        enqueues the rollouts).  The C routine releases the GIL."""
         if self.cursor <= 0:
             raise _lib.B200RLError("HostReplayIndex.select: no finished episodes indexed yet")
         a = int(args['maximum_episodes'])
         _lib.call("b200rl_select_windows_host", ctypes.c_void_p(self.table.data_ptr()), self.st.E, self.cursor, a,
-                  int(args['forward_steps']), int(seed) ^ 0x5E1EC7, self.draws, self.st.it + int(lookahead), self.st.D,
+                  int(args['forward_steps']), int(seed) ^ 0x5E1EC7, self.draws,
+                  int(self.st.it if it_now is None else it_now) + int(lookahead), self.st.D,
                   ctypes.c_void_p(out_pinned.data_ptr()), int(batch_size), self.n_threads)
         self.draws += 256
         return out_pinned

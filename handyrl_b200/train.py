@@ -71,56 +71,6 @@ def select_episode(episodes, args, rng=random):
     return ep_minimum
 
 
-def select_windows_host(ep_rows, batch_size, args, rng, it_now=None, depth=None, out=None):
-    """`select_episode` (handyrl/train.py:284-302) for a whole batch on the host, vectorised: `ep_rows` is the
-    host mirror of the finished-episode table, (L,4) int32 rows {slot, steps | win << 16, end_it lo, hi},
-    oldest first; `rng` a numpy Generator.  Returns (or fills `out` with) the (batch_size, 8) int32 window rows
-    that `make_batch_windows` consumes (upload them from pinned memory).
-
-    The reference's rejection loop accepts index i with probability a + i/M (a = 1 - (L-1)/M, M =
-    maximum_episodes); here i is drawn directly from that linear law by inverting its CDF (the half-step shift
-    makes the floor of the continuous draw exactly proportional to a + i/M), so one pass replaces the loop.
-    Rows that already left the trajectory ring are redrawn."""
-    L = len(ep_rows)
-    if L == 0:
-        raise _lib.B200RLError("select_windows_host: no finished episodes")
-    M, T = float(args['maximum_episodes']), int(args['forward_steps'])
-    n = min(L, int(M))                                                           # train.py:286
-    a = 1.0 - (L - 1) / M - 0.5 / M                                              # train.py:287, shifted half a step
-    total = a * n + n * n / (2 * M)
-    steps = ep_rows[:, 1] & 0xFFFF
-    end_lo = ep_rows[:, 2].view(np.uint32)
-    first_it = end_lo.astype(np.int64) + (ep_rows[:, 3].astype(np.int64) << 32) + 1 - steps
-
-    def draw(k):
-        u = rng.random(k) * total
-        x = M * (np.sqrt(a * a + 2.0 * u / M) - a) if a > 0 else np.sqrt(2.0 * M * u)
-        return np.minimum(x.astype(np.int64), n - 1)
-
-    idx = draw(batch_size)
-    if it_now is not None:
-        alive = (it_now - first_it) <= depth
-        for _ in range(64):
-            bad = np.nonzero(~alive[idx])[0]
-            if len(bad) == 0:
-                break
-            idx[bad] = draw(len(bad))
-        idx[~alive[idx]] = L - 1   # like the device kernel: give up on the newest episode
-    stp = steps[idx].astype(np.int64)
-    st = (rng.random(batch_size) * (1 + np.maximum(0, stp - T))).astype(np.int64)   # train.py:291-292
-    first = first_it[idx] + st
-    win = out if out is not None else np.empty((batch_size, 8), dtype=np.int32)
-    win[:, 0] = ep_rows[idx, 0]
-    win[:, 1] = (first & 0xFFFFFFFF).astype(np.uint32).view(np.int32)
-    win[:, 2] = (first >> 32).astype(np.int32)
-    win[:, 3] = np.minimum(st + T, stp) - st                                     # train.py:293
-    win[:, 4] = st
-    win[:, 5] = stp
-    win[:, 6] = (ep_rows[idx, 1] >> 16) & 3
-    win[:, 7] = rng.integers(0, 2, size=batch_size)                              # solo player, train.py:57-58
-    return win
-
-
 def _win_code(outcome):
     o0 = outcome[0]
     return 1 if o0 > 0 else (2 if o0 < 0 else 3)

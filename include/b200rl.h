@@ -24,6 +24,15 @@ extern "C" {
 const char* b200rl_last_error(void);
 int b200rl_version(void);
 
+/*
+ * Tuning knobs for A/B measurements and tests; not part of the reference's interface.  Every knob defaults to its
+ * environment variable (B200RL_<NAME IN CAPITALS>), read once per process; `set` = 0 returns the knob to its built-in
+ * default.  Knobs: rollout_chunk (plies per rollout ticket, 0 = static schedule), target_ws_stages (2..8),
+ * target_ws_row (256 | 512 bytes per row and fetch), target_ws_wide_rows (batch rows from which 512 is used),
+ * target_generic, target_no_dual, target_persistent (flags).  Results never depend on a knob.
+ */
+int b200rl_set_tuning(const char* name, int64_t value, int set);
+
 /* ------------------------------------------------------------------ */
 /* Part 3: off-policy target recursion — handyrl/losses.py:61-74       */
 /* ------------------------------------------------------------------ */
@@ -174,14 +183,18 @@ int b200rl_env_step_observe(int game, void* state, int64_t N, const int32_t* act
  *          (iteration it, slot i) at (i * D + it % D) * 32 bytes, or NULL
  *   ep_table : (E, 4) int32 ring of finished episodes {slot, steps | win << 16, end_it lo, hi}
  *   counters : uint64[8] {episodes, env steps, player0 wins, player1 wins, draws, ep_table cursor, -, -}
-  * Scheduling: (32-game group, 4-ply chunk) tickets from a library-owned scratch buffer per (device, stream),
- * allocated on first use (so the first call on a stream must not happen inside a CUDA-graph capture).
- * Results depend on (game, iteration) only.  Env B200RL_ROLLOUT_CHUNK=0 disables chunking (A/B measurements).
+ *   scratch : caller-owned device buffer of >= b200rl_env_rollout_scratch_bytes(N) bytes, 16-byte aligned, for
+ *          the (32-game group, 4-ply chunk) ticket counters; cleared by the launcher on `stream`, so one buffer
+ *          serves one stream at a time.  The library allocates nothing: the call is graph-capturable.
+ * Results depend on (game, iteration) only.  Tuning knob rollout_chunk = 0 disables chunking (A/B measurements).
  */
 int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_plies, uint64_t seed, uint64_t game_id_base,
                        uint64_t it0, float* out_main, float* out_scalar, float* out_amask, int32_t* out_action,
                        int64_t waves, void* traj, int64_t D, int32_t* ep_table, int64_t E, uint64_t* counters,
-                       void* stream);
+                       void* scratch, int64_t scratch_bytes, void* stream);
+
+/* Bytes of ticket scratch b200rl_env_rollout needs for N games (-1 for N < 0). */
+int64_t b200rl_env_rollout_scratch_bytes(int64_t N);
 
 /* ------------------------------------------------------------------ */
 /* Part 2: episode -> batch assembly — handyrl/train.py:33-133          */

@@ -115,7 +115,7 @@ def _hotpath_lib():
         h = ctypes.CDLL(path)
         h.orc_hotpath_create.restype = ctypes.c_void_p
         h.orc_hotpath_create.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint64,
-                                         ctypes.c_int]
+                                         ctypes.c_int, ctypes.c_double, ctypes.c_double]
         h.orc_hotpath_step.restype = ctypes.c_int64
         h.orc_hotpath_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         _hp = h
@@ -125,10 +125,11 @@ def _hotpath_lib():
 class HotPath:
     """G Geister games per thread: generation -> select_episode + make_batch -> UPGO/V-Trace targets, per step."""
 
-    def __init__(self, games_per_thread, plies, T, n_threads, replay_cap=256, seed=0):
+    def __init__(self, games_per_thread, plies, T, n_threads, replay_cap=256, seed=0, gamma=0.8, lmb=0.7):
         self.h = _hotpath_lib()
         self.G, self.plies, self.T, self.n_threads = games_per_thread, plies, T, n_threads
-        self.ctx = self.h.orc_hotpath_create(games_per_thread, plies, T, replay_cap, seed, n_threads)
+        self.ctx = self.h.orc_hotpath_create(games_per_thread, plies, T, replay_cap, seed, n_threads, float(gamma),
+                                             float(lmb))
 
     def step(self):
         out = (ctypes.c_int64 * 2)()

@@ -50,6 +50,7 @@ typedef struct {
     uint64_t seed;
     int64_t env_steps, batch_cells;
     double csum, sec[3]; /* seconds spent in generation / batching / targets */
+    double gamma, lmb;   /* args['gamma'], args['lambda'] of the training configuration */
     /* persistent state */
     orc_env* envs;
     hp_moment** cur;   /* per game: moments of the running episode */
@@ -73,7 +74,7 @@ static void hp_finish_episode(hp_thread* t, int g) {
     for (int p = 0; p < 2; ++p) { /* generation.py:73-77, accumulated in double like the Python float */
         double ret = 0.0;
         for (int i = n - 1; i >= 0; --i) {
-            ret = (double)ms[i].reward[p] + 0.8 * ret;
+            ret = (double)ms[i].reward[p] + t->gamma * ret;
             ms[i].ret[p] = (float)ret;
         }
     }
@@ -208,8 +209,8 @@ static void* hp_worker(void* arg) {
     hp_make_batch(t);
     double t2 = hp_now();
     const size_t n2 = (size_t)t->B * t->T * 2;
-    hp_targets_head(t, t->t_v, t->b_outcome, 0, NULL, 0.7f, 1.0f, t->t_tv, t->t_adv);
-    hp_targets_head(t, t->t_v + n2, t->b_ret, 1, t->b_reward, 0.7f, 0.8f, t->t_tv + n2, t->t_adv + n2);
+    hp_targets_head(t, t->t_v, t->b_outcome, 0, NULL, (float)t->lmb, 1.0f, t->t_tv, t->t_adv); /* train.py:245 */
+    hp_targets_head(t, t->t_v + n2, t->b_ret, 1, t->b_reward, (float)t->lmb, (float)t->gamma, t->t_tv + n2, t->t_adv + n2);
     double t3 = hp_now();
     t->sec[0] += t1 - t0; t->sec[1] += t2 - t1; t->sec[2] += t3 - t2;
     t->csum += t->t_tv[0] + t->t_adv[(size_t)t->B * t->T] + t->b_obs[7] + t->b_amask[3];
@@ -222,12 +223,14 @@ typedef struct {
     hp_thread* th;
 } hp_ctx;
 
-void* orc_hotpath_create(int G, int plies, int T, int replay_cap, uint64_t seed, int n_threads) {
+void* orc_hotpath_create(int G, int plies, int T, int replay_cap, uint64_t seed, int n_threads, double gamma,
+                         double lmb) {
     hp_ctx* c = (hp_ctx*)calloc(1, sizeof(hp_ctx));
     c->n_threads = n_threads;
     c->th = (hp_thread*)calloc((size_t)n_threads, sizeof(hp_thread));
     for (int i = 0; i < n_threads; ++i) {
         hp_thread* t = &c->th[i];
+        t->gamma = gamma; t->lmb = lmb;
         t->game = G_GEISTER; t->tid = i; t->G = G; t->plies = plies; t->T = T; t->replay_cap = replay_cap;
         t->rs = (seed + 1) * 0x9E3779B97F4A7C15ull + (uint64_t)i * 0xD1B54A32D192ED03ull + 1;
         t->envs = (orc_env*)calloc((size_t)G, sizeof(orc_env));

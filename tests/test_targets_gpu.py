@@ -99,6 +99,7 @@ def test_long_rows_ws_kernel(monkeypatch, B, T, P, rpp, vt, pt, head):
     """Rows longer than 64 steps run in the warp-specialised kernel (loader / compute / storer warps, mbarrier
     ring).  Both chunk widths and several ring depths must give the oracle's bits, with ragged last tiles, a
     partial first chunk (T % chunk != 0), per-player rhos, P = 1 and cs aliasing rhos."""
+    from handyrl_b200 import _lib
     from handyrl_b200.losses import compute_target_pair
     d = target_inputs(B, T, P, head, rpp, seed=B + T + 7)
     rt, _ = targets_np.compute_target(vt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['cs'])
@@ -107,13 +108,15 @@ def test_long_rows_ws_kernel(monkeypatch, B, T, P, rpp, vt, pt, head):
     a = (g['values'], g['returns'], g['rewards'], g['lmb'], g['gamma'])
     for row in ('256', '512'):
         for stages in ('2', '5'):
-            monkeypatch.setenv('B200RL_TARGET_WS_ROW', row)
-            monkeypatch.setenv('B200RL_TARGET_WS_STAGES', stages)
-            t1, a1 = compute_target_pair(vt, pt, *a, g['rhos'], g['cs'])
+            _lib.set_tuning('target_ws_row', int(row))
+            _lib.set_tuning('target_ws_stages', int(stages))
+            try:
+                t1, a1 = compute_target_pair(vt, pt, *a, g['rhos'], g['cs'])
+            finally:
+                _lib.set_tuning('target_ws_row', None)
+                _lib.set_tuning('target_ws_stages', None)
             _close(t1, np.asarray(rt))
             _close(a1, np.asarray(ra))
-    monkeypatch.delenv('B200RL_TARGET_WS_ROW')
-    monkeypatch.delenv('B200RL_TARGET_WS_STAGES')
     if 'VTRACE' in (vt, pt):
         rt2, _ = targets_np.compute_target(vt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['rhos'])
         _, ra2 = targets_np.compute_target(pt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['rhos'])
