@@ -366,7 +366,14 @@ def main():
         win_pin = [torch.empty(B, 8, dtype=torch.int32).pin_memory() for _ in range(DEPTH)]
         win_devs = [torch.empty(B, 8, dtype=torch.int32, device=dev) for _ in range(DEPTH)]
         met_pin = [torch.zeros(4, dtype=torch.float32).pin_memory() for _ in range(DEPTH)]
-        copy_stream = torch.cuda.Stream(device=dev)      # PCIe traffic runs beside the kernels, ordered by events
+        # PCIe traffic runs beside the kernels on its own streams, ordered by events.  Two streams: the D2H of a
+        # rollout's rows has to wait for that rollout, the H2D of this step's windows must not queue behind it
+        # (on one copy stream it did, and the GPU idled 0.16 ms per step waiting for its windows).  The summary of
+        # the targets (4 means + D2H) runs on a third stream beside the next rollout.
+        copy_stream = torch.cuda.Stream(device=dev)      # D2H: counters + finished-episode rows
+        h2d_stream = torch.cuda.Stream(device=dev)       # H2D: windows
+        sum_stream = torch.cuda.Stream(device=dev)       # target summary + its D2H
+        ev_tail = [torch.cuda.Event() for _ in range(DEPTH)]
         ev_roll = [torch.cuda.Event() for _ in range(DEPTH)]
         ev_h2d = [torch.cuda.Event() for _ in range(DEPTH)]
         ev_done = [torch.cuda.Event() for _ in range(DEPTH)]
@@ -430,16 +437,21 @@ def main():
                 if hs["err"] is not None:
                     raise hs["err"]
                 t_c = pc()
-                with torch.cuda.stream(copy_stream):                            # H2D of this step's windows
+                with torch.cuda.stream(h2d_stream):                             # H2D of this step's windows
                     win_devs[s].copy_(win_pin[s], non_blocking=True)
                     ev_h2d[s].record()
                 torch.cuda.current_stream().wait_event(ev_h2d[s])
                 evk[3].record()
                 (tv, av), (tr, ar) = step_tail(k, win_devs[s])
                 evk[4].record()
-                met_pin[s].copy_(torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()]), non_blocking=True)
+                ev_tail[s].record()
+                with torch.cuda.stream(sum_stream):                             # result of the step -> host
+                    sum_stream.wait_event(ev_tail[s])
+                    for t_ in (tv, av, tr, ar):
+                        t_.record_stream(sum_stream)
+                    met_pin[s].copy_(torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()]), non_blocking=True)
+                    ev_done[s].record()
                 evk[5].record()
-                ev_done[s].record()
             t_d = pc()
             if k >= 2 * LOOK:                                                   # result of step k-2 (D2H landed long ago)
                 ev_done[(k - LOOK) % DEPTH].synchronize()
@@ -486,11 +498,11 @@ def main():
                "selector_threads": index.n_threads,
                "gpu_ms_per_step": {name: round(sum(e_[i].elapsed_time(e_[i + 1]) for e_ in timed_evs) / len(timed_evs), 4)
                                    for i, name in enumerate(("rollout", "enqueue_gap", "wait_h2d_windows",
-                                                             "make_batch_targets", "summary_d2h"))},
+                                                             "make_batch_targets", "gap_after_targets"))},
                "note": "per step, calling thread (enqueue only): BatchGenerator.rollout; D2H of the counters and the "
-                       "new finished-episode rows; pinned H2D of the windows drawn two steps earlier (copy stream, "
-                       "event-ordered); make_batch_windows; compute_target_heads (value + return head, one launch); D2H "
-                       "of the target summary, read two steps late.  Background thread: HostReplayIndex.commit + "
+                       "new finished-episode rows (copy stream); pinned H2D of the windows drawn two steps earlier (second copy "
+                       "stream, event-ordered); make_batch_windows; compute_target_heads (value + return head, one launch); "
+                       "target summary + its D2H on a third stream, read two steps late.  Background thread: HostReplayIndex.commit + "
                        "select (b200rl_select_windows_host, replay index on the host).  Moments stay in HBM (the "
                        "trajectory ring is the replay buffer).  Wall clock incl. all host work."}
 

@@ -35,6 +35,7 @@ Knob g_knobs[B200RL_TUNE_COUNT] = {
     {"target_generic", "B200RL_TARGET_GENERIC", {0}, {0}},
     {"target_no_dual", "B200RL_TARGET_NO_DUAL", {0}, {0}},
     {"target_persistent", "B200RL_TARGET_PERSISTENT", {0}, {0}},
+    {"emit_tma", "B200RL_EMIT_TMA", {0}, {0}},
 };
 }  // namespace
 

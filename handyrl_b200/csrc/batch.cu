@@ -269,9 +269,14 @@ __device__ __forceinline__ void pack_rows(uint32_t* flat, int lane, int Po, int 
     if (Po == 2) flat_row_store<NB, RW>(flat, r0 + 1, bits[1], t0, r0 + 1 == n_rows - 1, t1);
 }
 
-template <class G>
+// TMA = the big tensors leave through staged bulk copies (emit_flat_f32_tma) instead of STG.128 (emit_flat_f32);
+// dynamic shared memory then holds WARPS x MB_NBUF x MB_CH bytes of staging.
+constexpr int MB_CH = 4096, MB_NBUF = 3;
+
+template <class G, bool TMA>
 __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
     __shared__ BatchCta<G> cta;
+    extern __shared__ __align__(128) unsigned char mb_dyn_smem[];
     nibble_table_init(cta.tbl_obs, 0.f, 1.f, threadIdx.x);
     nibble_table_init(cta.tbl_amask, 1e32f, 0.f, threadIdx.x);
     nibble_table_init(cta.tbl_policy, 0.f, -1e32f, threadIdx.x);
@@ -415,6 +420,17 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
         }
     }
     __syncwarp();
+    if (TMA) {
+        TmaStage<MB_CH, MB_NBUF> ts;
+        ts.buf = reinterpret_cast<float4*>(mb_dyn_smem) + (size_t)(threadIdx.x >> 5) * MB_NBUF * (MB_CH / 16);
+        ts.c = 0;
+        emit_flat_f32_tma<G::OBITS>(st.obs, p.obs_main + c0 * Po * G::OBITS, ng, lane, 0.f, 1.f, ts);
+        if (G::SBITS > 0) emit_flat_f32_tma<SB>(st.scalar, p.obs_scalar + c0 * Po * G::SBITS, ng, lane, 0.f, 1.f, ts);
+        emit_flat_f32_tma<G::A>(st.legal, p.amask + c0 * Po * G::A, ng, lane, 1e32f, 0.f, ts);
+        if (rnd_policy) emit_flat_f32_tma<G::A>(st.illegal, p.policy + c0 * Po * G::A, ng, lane, 0.f, -1e32f, ts);
+        ts.drain(lane);
+        return;
+    }
     emit_flat_f32<G::OBITS>(st.obs, cta.tbl_obs, p.obs_main + c0 * Po * G::OBITS, ng, lane, 0.f, 1.f);
     if (G::SBITS > 0) emit_flat_f32<SB>(st.scalar, cta.tbl_obs, p.obs_scalar + c0 * Po * G::SBITS, ng, lane, 0.f, 1.f);
     emit_flat_f32<G::A>(st.legal, cta.tbl_amask, p.amask + c0 * Po * G::A, ng, lane, 1e32f, 0.f);
@@ -551,7 +567,23 @@ int launch_make_batch(const BatchParams& p, cudaStream_t stream) {
     B200RL_REQUIRE(G::SBITS == 0 || p.obs_scalar, "make_batch: this game needs obs_scalar");
     const int64_t ncell = p.B * p.T;
     const int Po = p.mode == MB_ALL ? 2 : 1;
-    k_make_batch<G><<<grid_for(ncell), BLK, 0, stream>>>(p);
+    // staged bulk stores for the games whose tiles are large (Geister: 32 KB of observation per warp tile); the
+    // 3 KB TicTacToe tiles stay on STG.128.  Knob emit_tma = 0 / 1 forces either (A/B measurements, tests).
+    long long knob = 0;
+    const bool tma = b200rl_tuning(B200RL_TUNE_EMIT_TMA, &knob) ? knob != 0 : G::OBITS >= 128;
+    if (tma) {
+        constexpr int DYN = WARPS * MB_NBUF * MB_CH;
+        static std::atomic<int> attr_set[64];
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (attr_set[dev & 63].load(std::memory_order_relaxed) == 0) {
+            cudaFuncSetAttribute(k_make_batch<G, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DYN);
+            attr_set[dev & 63].store(1, std::memory_order_relaxed);
+        }
+        k_make_batch<G, true><<<grid_for(ncell), BLK, DYN, stream>>>(p);
+    } else {
+        k_make_batch<G, false><<<grid_for(ncell), BLK, 0, stream>>>(p);
+    }
     if (p.logits) {
         const int64_t rows = ncell * Po;
         k_policy_from_logits<G><<<(int)((rows + WARPS - 1) / WARPS), BLK, 0, stream>>>(p);

@@ -150,3 +150,65 @@ __device__ __forceinline__ void emit_flat_f32(const uint32_t* __restrict__ flat,
     // tail (< 4 floats) of a partial tile
     for (int e = (n4 << 2) + lane; e < total; e += 32) out_tile[e] = ((flat[e >> 5] >> (e & 31)) & 1u) ? v1 : v0;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// TMA variant of the streaming loop (profiles/r2_probe_write_tma.txt: 7.04 -> 7.3-7.45 TB/s on the same tiles).
+// The warp expands the tile chunk by chunk into a private ring of NBUF staging buffers in shared memory
+// (st.shared.v4, lane q -> float4 q: conflict-free) and ONE lane hands each finished chunk to the copy engine:
+//     cp.async.bulk.global.shared::cta.bulk_group   (SASS UBLKCP.G.S)
+// so the global stores leave the LSU pipe and reach L2 as CH-byte bursts.  A buffer is reused once the bulk group
+// that read it has completed (cp.async.bulk.wait_group.read).  Bulk groups are tracked per thread: lane 0 issues and
+// waits for all of them, the other lanes follow through __syncwarp.
+// ---------------------------------------------------------------------------------------------------------------
+template <int CH, int NBUF>
+struct TmaStage {
+    static_assert(CH % 16 == 0 && NBUF >= 1, "chunks are multiples of 16 bytes");
+    float4* buf;   // NBUF x CH bytes, 128-byte aligned, private to the warp
+    int c;         // chunks committed so far (all lanes keep the same count)
+
+    __device__ __forceinline__ float4* acquire(int lane) {
+        if (c >= NBUF) {   // the group that last read this buffer is NBUF commits old
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NBUF - 1) : "memory");
+            __syncwarp();
+        }
+        return buf + (c % NBUF) * (CH / 16);
+    }
+    // all lanes have written their part of `b` (generic proxy) -> visible to the async proxy -> bulk copy
+    __device__ __forceinline__ void commit(int lane, void* gdst, const float4* b, int bytes) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+                         "r"((uint32_t)__cvta_generic_to_shared(b)), "r"(bytes)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        ++c;
+    }
+    // before the CTA exits (or the buffers are used for anything else): every bulk read of shared memory is done
+    __device__ __forceinline__ void drain(int lane) {
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+    }
+};
+
+// Same bytes as emit_flat_f32 (tile base 16-byte aligned).
+template <int NB, int CH, int NBUF>
+__device__ __forceinline__ void emit_flat_f32_tma(const uint32_t* __restrict__ flat, float* __restrict__ out_tile,
+                                                  int rows, int lane, float v0, float v1, TmaStage<CH, NBUF>& st) {
+    constexpr int CH4 = CH / 16;
+    static_assert(CH4 % 32 == 0, "a chunk is a whole number of warp-wide float4 rows");
+    const int total = rows * NB;
+    const int n4 = total >> 2;
+    const int sh = (lane & 7) << 2;                      // q0 and the lane stride are multiples of 8 float4
+#pragma unroll 1
+    for (int q0 = 0; q0 < n4; q0 += CH4) {
+        const int nq = min(CH4, n4 - q0);
+        float4* b = st.acquire(lane);
+        const uint32_t* fw = flat + ((q0 + lane) >> 3);
+#pragma unroll 4
+        for (int q = lane; q < nq; q += 32) b[q] = nibble_expand(fw[(q - lane) >> 3] >> sh, nullptr, v0, v1);
+        st.commit(lane, out_tile + (size_t)q0 * 4, b, nq * 16);
+    }
+    for (int e = (n4 << 2) + lane; e < total; e += 32) out_tile[e] = ((flat[e >> 5] >> (e & 31)) & 1u) ? v1 : v0;
+}

@@ -302,17 +302,21 @@ class BatchGenerator:
         return hidden
 
     # -- window selection on the device (Batcher.select_episode, train.py:284-302) -------
-    def select_windows(self, batch_size, args, seed=None, out=None):
+    def select_windows(self, batch_size, args, seed=None, out=None, counters=None, it_now=None):
         """(batch_size, 8) int32 windows for `train.make_batch_windows`, drawn on the device from the
-        finished-episode table without a host round trip."""
+        finished-episode table without a host round trip.  `counters` may be a SNAPSHOT of the store's counters (a
+        caller that trains beside a running generation wave must not read the live cursor: a row is written after
+        its cursor increment) and `it_now` the ring iteration the windows must survive until (default: now)."""
         st, env = self.store, self.env
         if out is None:
             out = torch.empty(batch_size, 8, dtype=torch.int32, device=env.device)
         self._draws = getattr(self, "_draws", 0)
+        ctr = st.counters if counters is None else counters
         with torch.cuda.device(env.device):
-            _lib.call("b200rl_select_windows", _ptr(st.ep_table), st.E, _ptr(st.counters),
+            _lib.call("b200rl_select_windows", _ptr(st.ep_table), st.E, _ptr(ctr),
                       int(args['maximum_episodes']), int(args['forward_steps']),
-                      int(self.seed if seed is None else seed) ^ 0x5E1EC7, self._draws, st.it, st.D, _ptr(out),
+                      int(self.seed if seed is None else seed) ^ 0x5E1EC7, self._draws,
+                      int(st.it if it_now is None else it_now), st.D, _ptr(out),
                       int(batch_size), env._stream())
         self._draws += 256
         return out

@@ -178,12 +178,17 @@ def flat_grads(params):
     return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in params])
 
 
-def allreduce_gradients(params, group=None):
-    """Average gradients over the ranks with ONE all-reduce of a flat fp32 bucket (GeisterNet: 0.94 MB)."""
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
-        return
+def allreduce_gradients(params, group=None, extra=None):
+    """Average gradients over the ranks with ONE all-reduce of a flat fp32 bucket (GeisterNet: 0.94 MB).
+    `extra` (a list of floats) rides in the same bucket and comes back as the mean over the ranks - the learner
+    uses it for the data count of the step, so that every replica applies the same learning rate."""
+    distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    if not distributed:
+        return list(extra) if extra is not None else None
     params = [p for p in params if p.requires_grad]
     bucket = flat_grads(params)
+    if extra is not None:
+        bucket = torch.cat([bucket, torch.tensor(list(extra), dtype=bucket.dtype, device=bucket.device)])
     dist.all_reduce(bucket, op=dist.ReduceOp.SUM, group=group)
     bucket /= dist.get_world_size(group)
     off = 0
@@ -195,6 +200,7 @@ def allreduce_gradients(params, group=None):
         else:
             p.grad.copy_(g)
         off += n
+    return bucket[off:].tolist() if extra is not None else None
 
 
 def broadcast_weights(model, src=0, group=None):
@@ -227,6 +233,7 @@ class DataParallelLearner:
         lr = self.default_lr * self.data_cnt_ema
         self.optimizer = torch.optim.Adam(self.params, lr=lr, weight_decay=1e-5) if self.params else None
         self.steps = 0
+        self.batch_cnt, self.data_cnt = 0, 0.0        # of the running epoch (train.py:370, 396)
         broadcast_weights(model, 0, group)
 
     def train_step(self, batch, hidden=None):
@@ -234,11 +241,22 @@ class DataParallelLearner:
         losses, dcnt = compute_loss(batch, self.model, hidden, self.args)
         self.optimizer.zero_grad()
         losses['total'].backward()
-        allreduce_gradients(self.params, self.group)
+        # the step's data count travels in the gradient bucket: all replicas see the same (mean) count and therefore
+        # apply the same learning rate below - rank-local counts would let the replicas drift apart between the
+        # per-epoch weight broadcasts
+        dcnt_mean = allreduce_gradients(self.params, self.group, extra=[dcnt])[0]
         torch.nn.utils.clip_grad_norm_(self.params, 4.0)
         self.optimizer.step()
         self.steps += 1
-        self.data_cnt_ema = self.data_cnt_ema * 0.8 + dcnt * 0.2   # reference: updated per epoch from the batch counts
-        for g in self.optimizer.param_groups:
-            g['lr'] = self.default_lr * self.data_cnt_ema / (1 + self.steps * 1e-5)
+        self.batch_cnt += 1
+        self.data_cnt += dcnt_mean
         return {k: float(v.detach()) for k, v in losses.items()}, dcnt
+
+    def end_epoch(self):
+        """Learning-rate schedule of handyrl/train.py:396-398, applied once per epoch like the reference:
+        data_cnt_ema <- 0.8 * ema + 0.2 * (mean data count per batch of the epoch); lr = 3e-8 * ema / (1 + steps * 1e-5)."""
+        if self.batch_cnt > 0:
+            self.data_cnt_ema = self.data_cnt_ema * 0.8 + self.data_cnt / (1e-2 + self.batch_cnt) * 0.2
+            for g in self.optimizer.param_groups:
+                g['lr'] = self.default_lr * self.data_cnt_ema / (1 + self.steps * 1e-5)
+        self.batch_cnt, self.data_cnt = 0, 0.0

@@ -91,21 +91,33 @@ def make_batch_from_reference_episodes(episodes, args, device=None):
     oc_dev = torch.from_numpy(outcome).to(dev)
     out = {}
     for key in per_ep[0]:
-        rag = np.concatenate([r[key] for r in per_ep])               # (sum T', ...)
-        tail = rag.shape[1:]
-        words = int(np.prod(tail)) * (2 if rag.dtype == np.int64 else 1)
-        src = torch.from_numpy(np.ascontiguousarray(rag)).pin_memory().to(dev, non_blocking=True)
-        dst = torch.empty((B, T) + tail, dtype=src.dtype, device=dev)
+        rag = np.ascontiguousarray(np.concatenate([r[key] for r in per_ep]))   # (sum T', ...)
+        tail, dt = rag.shape[1:], rag.dtype
         if key == 'value':
             fill_rows, fill = oc_dev, 0.0                            # value <- outcome (train.py:96)
         else:
             fill_rows = None
             fill = 0.0 if isinstance(key, tuple) else _FILL[key]
+        if fill not in (None, 0.0) or fill_rows is not None:
+            if dt != np.float32:                                     # the fill is a 32-bit float pattern
+                raise _lib.B200RLError("make_batch: '%s' must be float32 (got %s)" % (key, dt))
+        # The kernel moves rows as 4-byte words whatever the element type (uint8 images, bool planes, float64
+        # vectors ... - the reference's to_torch keeps the numpy dtype, model.py:16-19): rows are handed over as raw
+        # bytes, padded on the host to a multiple of 4 when needed.  Observation padding is all-zero bytes.
+        row_bytes = int(np.prod(tail, dtype=np.int64)) * dt.itemsize
+        raw = rag.view(np.uint8).reshape(rag.shape[0], row_bytes)
+        pad = (-row_bytes) % 4
+        if pad:
+            raw = np.pad(raw, ((0, 0), (0, pad)))
+        src = torch.from_numpy(raw).pin_memory().to(dev, non_blocking=True)
+        dst = torch.empty((B, T, row_bytes + pad), dtype=torch.uint8, device=dev)
         bits = 0 if fill is None else int(np.float32(fill).view(np.uint32))
         with torch.cuda.device(dev):
             _lib.call("b200rl_pad_stack", _ptr(src), _ptr(off), _ptr(fill_rows), ctypes.c_uint32(bits), _ptr(dst),
-                      B, T, words, _lib.stream_ptr())
-        out[key] = dst
+                      B, T, (row_bytes + pad) // 4, _lib.stream_ptr())
+        if pad:
+            dst = dst[..., :row_bytes].contiguous()
+        out[key] = dst.view(torch.from_numpy(np.empty(0, dt)).dtype).reshape((B, T) + tail)
     obs_keys = [k for k in out if isinstance(k, tuple)]
     if len(obs_keys) == 1 and obs_keys[0][1] is None:
         observation = out[obs_keys[0]]

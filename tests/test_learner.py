@@ -95,8 +95,9 @@ def _dp_worker(rank, world, port, q):
     out = net(x)
     (out['policy'].sum() * (rank + 1) + out['value'].sum()).backward()
     local = [p.grad.clone() for p in net.parameters()]
-    allreduce_gradients(list(net.parameters()))
-    ok = True
+    extra = allreduce_gradients(list(net.parameters()), extra=[100.0 * (rank + 1), 7.0])
+    # the step's data count rides in the bucket and comes back as the mean over the ranks (same lr on every replica)
+    ok = abs(extra[0] - 100.0 * (world + 1) / 2) < 1e-3 and abs(extra[1] - 7.0) < 1e-5
     for p, g in zip(net.parameters(), local):
         gs = [torch.zeros_like(g) for _ in range(world)]
         dist.all_gather(gs, g)
@@ -128,4 +129,5 @@ def test_single_process_learner_helpers_are_noops():
     w = [p.detach().clone() for p in net.parameters()]
     broadcast_weights(net)
     allreduce_gradients(list(net.parameters()))
+    assert allreduce_gradients(list(net.parameters()), extra=[3.0]) == [3.0]
     assert all(torch.equal(a, b) for a, b in zip(w, net.parameters()))

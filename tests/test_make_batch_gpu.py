@@ -199,3 +199,78 @@ def test_reference_format_episodes_match_reference(cases, name):
     for k, ref in c['out'].items():
         assert out[k].shape == ref.shape and out[k].dtype == ref.dtype, (k, out[k].shape, ref.shape, out[k].dtype)
         np.testing.assert_array_equal(out[k], ref, err_msg=k)
+
+
+def _custom_obs_episodes(n_ep, rng):
+    """Reference-wire episodes of a made-up two-player game whose observation is a dict of a uint8 image with an odd
+    row size (2x3 bytes), a float64 vector and a bool plane (the reference's to_torch keeps numpy dtypes,
+    model.py:16-19)."""
+    eps = []
+    for e in range(n_ep):
+        steps = int(rng.integers(2, 9))
+        moments = []
+        for t in range(steps):
+            turn = t % 2
+            m = {k: {0: None, 1: None} for k in ('observation', 'policy', 'action_mask', 'action', 'value', 'reward',
+                                                'return')}
+            m['observation'][turn] = {'img': rng.integers(0, 256, (2, 3), dtype=np.uint8),
+                                      'vec': rng.standard_normal(5),
+                                      'flag': rng.integers(0, 2, (3,)).astype(bool)}
+            pol = rng.standard_normal(7).astype(np.float32)
+            am = np.where(rng.random(7) < 0.5, 0, 1e32).astype(np.float32)
+            m['policy'][turn], m['action_mask'][turn], m['action'][turn] = pol - am, am, int(rng.integers(0, 7))
+            m['value'][turn] = np.array([rng.standard_normal()], np.float32)
+            for p in (0, 1):
+                m['reward'][p], m['return'][p] = float(rng.standard_normal()), float(rng.standard_normal())
+            m['turn'] = [turn]
+            moments.append(m)
+        eps.append({'args': {}, 'steps': steps, 'outcome': {0: 1, 1: -1},
+                    'moment': [bz2.compress(pickle.dumps(moments[i:i + 4])) for i in range(0, steps, 4)]})
+    return eps
+
+
+def test_reference_wire_path_keeps_any_observation_dtype():
+    """pad_stack rows are raw bytes - uint8 / bool / float64 observation leaves must come back
+    with their dtype, padded with zeros, bit-identical to the numpy oracle."""
+    from handyrl_b200.train import make_batch, select_episode
+    rng = np.random.default_rng(7)
+    eps = _custom_obs_episodes(12, rng)
+    args = {'turn_based_training': True, 'observation': False, 'gamma': 0.8, 'forward_steps': 6, 'compress_steps': 4,
+            'maximum_episodes': 100}
+    prng = random.Random(3)
+    wins = [select_episode(eps, args, prng) for _ in range(20)]
+    out = _flatten(make_batch(wins, args))
+    ref = make_batch_np.make_batch(wins, args)
+    assert out['observation.img'].dtype == np.uint8 and out['observation.vec'].dtype == np.float64
+    assert out['observation.flag'].dtype == np.bool_
+    assert set(out) == set(ref)
+    for k in ref:
+        assert out[k].shape == ref[k].shape and out[k].dtype == ref[k].dtype, (k, out[k].dtype, ref[k].dtype)
+        np.testing.assert_array_equal(out[k], ref[k], err_msg=k)
+
+
+@pytest.mark.parametrize("game,B,T,mode", [('Geister', 3, 5, 'turn'), ('Geister', 7, 9, 'all'), ('CIGeister', 33, 16, 'turn'),
+                                           ('Geister', 5, 7, 'solo'), ('TicTacToe', 9, 3, 'turn'),
+                                           ('ParallelTicTacToe', 5, 5, 'solo')])
+def test_bulk_store_emit_equals_stg_emit(game, B, T, mode):
+    """k_make_batch<G, TMA>: the staged bulk-store path (cp.async.bulk.global.shared::cta) must write exactly the
+    bytes of the STG.128 path that the golden cases pin - including ragged last tiles with an odd number of rows
+    (chunk sizes that are not multiples of 16 bytes end in plain stores)."""
+    from handyrl_b200 import _lib
+    from handyrl_b200.generation import BatchGenerator
+    from handyrl_b200.train import make_batch_windows
+    gen = BatchGenerator(game, 96, seed=4, depth=512)
+    gen.rollout(300 if 'Geister' in game else 40)
+    args = {'turn_based_training': mode != 'solo', 'observation': mode == 'all', 'gamma': 0.8, 'forward_steps': T,
+            'compress_steps': 4, 'maximum_episodes': 1000}
+    w = gen.select_windows(B, args, seed=2)
+    outs = []
+    for knob in (0, 1):
+        _lib.set_tuning('emit_tma', knob)
+        try:
+            outs.append(_flatten(make_batch_windows(gen.store, w, args)))
+        finally:
+            _lib.set_tuning('emit_tma', None)
+    for k in outs[0]:
+        np.testing.assert_array_equal(outs[0][k], outs[1][k], err_msg=k)
+    assert float(np.abs(outs[0]['action_mask']).sum()) > 0
