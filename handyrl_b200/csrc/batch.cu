@@ -568,7 +568,10 @@ int launch_make_batch(const BatchParams& p, cudaStream_t stream) {
     const int64_t ncell = p.B * p.T;
     const int Po = p.mode == MB_ALL ? 2 : 1;
     // staged bulk stores for the games whose tiles are large (Geister: 32 KB of observation per warp tile); the
-    // 3 KB TicTacToe tiles stay on STG.128.  Knob emit_tma = 0 / 1 forces either (A/B measurements, tests).
+    // 3 KB TicTacToe tiles stay on STG.128.  Measured on the bench workload: 0.943 -> 0.939 ms (two A/B pairs,
+    // profiles/r2_tma_emit_ab.md) - within 1 %, although the isolated emit probe gains 4-6 %: what holds make_batch
+    // at 6.4 TB/s is the record gather inside the write stream, not the store path.  Knob emit_tma = 0 / 1 forces
+    // either (A/B measurements, tests).
     long long knob = 0;
     const bool tma = b200rl_tuning(B200RL_TUNE_EMIT_TMA, &knob) ? knob != 0 : G::OBITS >= 128;
     if (tma) {

@@ -104,11 +104,14 @@ __global__ void __launch_bounds__(BLK) k_info(const uint32_t* state, int64_t N, 
     out[4 * i + 3] = G::terminal(s) ? (o0 > 0 ? 1 : (o1 > 0 ? 2 : 3)) : 0;
 }
 
+constexpr int RO_CH = 4096, RO_NBUF = 3;   // staging of the bulk-store emit path of k_rollout<G, true>
+
 // Pack this lane's bits into the warp's flat strings, then let the warp stream the tile out.
 template <class G>
 __device__ __forceinline__ void emit_views(CtaStage<G>& cta, int warp, const typename G::State& s, bool valid,
                                            int view, int64_t g0, int ng, int lane, float* out_main,
-                                           float* out_scalar, float* out_amask, uint32_t* out_bits) {
+                                           float* out_scalar, float* out_amask, uint32_t* out_bits,
+                                           TmaStage<RO_CH, RO_NBUF>* tma = nullptr) {
     WarpStage<G>& st = cta.w[warp];
     constexpr int SB = G::SBITS > 0 ? G::SBITS : 1;
     const bool want_obs = out_main || (G::SBITS > 0 && out_scalar);
@@ -146,6 +149,13 @@ __device__ __forceinline__ void emit_views(CtaStage<G>& cta, int warp, const typ
         }
     }
     __syncwarp();
+    if (tma) {   // staged bulk stores (emit.cuh); the flat strings are free again when this returns
+        if (out_main) emit_flat_f32_tma<G::OBITS>(st.obs, out_main + g0 * G::OBITS, ng, lane, 0.f, 1.f, *tma);
+        if (G::SBITS > 0 && out_scalar) emit_flat_f32_tma<SB>(st.scalar, out_scalar + g0 * G::SBITS, ng, lane, 0.f, 1.f, *tma);
+        if (out_amask) emit_flat_f32_tma<G::A>(st.legal, out_amask + g0 * G::A, ng, lane, 1e32f, 0.f, *tma);
+        __syncwarp();
+        return;
+    }
     if (out_main) emit_flat_f32<G::OBITS>(st.obs, cta.tbl_obs, out_main + g0 * G::OBITS, ng, lane, 0.f, 1.f);
     if (G::SBITS > 0 && out_scalar)
         emit_flat_f32<SB>(st.scalar, cta.tbl_obs, out_scalar + g0 * G::SBITS, ng, lane, 0.f, 1.f);
@@ -310,9 +320,17 @@ __device__ __forceinline__ void ep_flush(const RolloutParams& p, const int4* buf
 // write stream: 6.3 TB/s static, 7.2 TB/s with dynamic assignment); with tickets the fast SMs take more chunks.
 // A ticket only ever waits for a ticket that a RUNNING warp claimed earlier, so there is no deadlock whatever
 // the number of resident CTAs.  Results depend on (game, iteration) only, not on which warp ran a ticket.
-template <class G>
-__global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
+// TMA: the moment tensors leave through staged bulk copies (cp.async.bulk, emit.cuh) instead of STG.128; dynamic
+// shared memory then holds WARPS x RO_NBUF x RO_CH bytes of staging.  Besides moving the stores off the LSU pipe
+// this takes them out of the scope of the ticket fence (__threadfence orders the thread's own stores - the 64-byte
+// states other tickets wait for -, not the copy engine's writes, which nobody reads before the kernel ends).
+template <class G, bool TMA>
+__global__ void __launch_bounds__(BLK, TMA ? 5 : 8) k_rollout(const RolloutParams p) {
     __shared__ CtaStage<G> stage;
+    extern __shared__ __align__(128) unsigned char ro_dyn_smem[];
+    TmaStage<RO_CH, RO_NBUF> tma_stage;
+    tma_stage.buf = reinterpret_cast<float4*>(ro_dyn_smem) + (size_t)(threadIdx.x >> 5) * RO_NBUF * (RO_CH / 16);
+    tma_stage.c = 0;
     // write combining of the trajectory records: 4 plies x 32 B per game = one 128-byte line of the slot-major
     // ring, staged as [ply & 3][half][lane] 16-byte units (conflict-free) and flushed every 4th ply
     __shared__ uint4 rec_stage[WARPS][4][2][32];
@@ -400,7 +418,8 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
                 emit_views<G>(stage, warp, s, valid, B200RL_VIEW_TURN, g0, ng, lane,
                               p.out_main ? p.out_main + wv * p.N * G::OBITS : nullptr,
                               p.out_scalar ? p.out_scalar + wv * p.N * G::SBITS : nullptr,
-                              p.out_amask ? p.out_amask + wv * p.N * G::A : nullptr, nullptr);
+                              p.out_amask ? p.out_amask + wv * p.N * G::A : nullptr, nullptr,
+                              TMA ? &tma_stage : nullptr);
             }
             bool term = false;
             uint32_t wincode = 0;
@@ -487,6 +506,7 @@ __global__ void __launch_bounds__(BLK, 8) k_rollout(const RolloutParams p) {
         }
     }
     publish();
+    if (TMA) tma_stage.drain(lane);   // the copy engine still reads the staging buffers of the last chunks
     if (p.counters) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -510,17 +530,33 @@ inline int grid_for(int64_t N) { return (int)((N + BLK - 1) / BLK); }
 // persistent grid: as many CTAs as are resident at once (8 per SM for Geister at 128 registers, more for TicTacToe)
 template <class G>
 void launch_rollout(const RolloutParams& p, int64_t want, int dev, int sms, cudaStream_t stream) {
-    static std::atomic<int> per_sm_dev[64];   // per device: the occupancy query is a property of (kernel, device)
-    std::atomic<int>& slot = per_sm_dev[dev & 63];
+    // Staged bulk stores are OFF by default here: measured on the bench workload they are 1 % SLOWER than STG.128
+    // (0.641 -> 0.648 ms, profiles/r2_tma_emit_ab.md) although the isolated emit probe gains 4-6 %
+    // (profiles/r2_probe_write_tma.txt) - the 168-register variant holds 10 warps per SM instead of 16 and the
+    // rollout is not bound by its store instructions.  Knob emit_tma = 1 selects them (tests cover both).
+    long long knob = 0;
+    const bool has_out = p.out_main || p.out_scalar || p.out_amask;
+    const bool tma = has_out && b200rl_tuning(B200RL_TUNE_EMIT_TMA, &knob) && knob != 0;
+    constexpr int DYN = WARPS * RO_NBUF * RO_CH;
+    static std::atomic<int> per_sm_dev[64][2];   // per device: the occupancy query is a property of (kernel, device)
+    std::atomic<int>& slot = per_sm_dev[dev & 63][tma ? 1 : 0];
     int per_sm = slot.load(std::memory_order_relaxed);
     if (per_sm == 0) {
         int n = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_rollout<G>, BLK, 0) != cudaSuccess || n < 1) n = 8;
+        cudaError_t e;
+        if (tma) {
+            cudaFuncSetAttribute(k_rollout<G, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DYN);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_rollout<G, true>, BLK, DYN);
+        } else {
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_rollout<G, false>, BLK, 0);
+        }
+        if (e != cudaSuccess || n < 1) n = tma ? 5 : 8;
         per_sm = n;
         slot.store(n, std::memory_order_relaxed);
     }
     const int grid = (int)min(want, (int64_t)sms * per_sm);
-    k_rollout<G><<<grid, BLK, 0, stream>>>(p);
+    if (tma) k_rollout<G, true><<<grid, BLK, DYN, stream>>>(p);
+    else k_rollout<G, false><<<grid, BLK, 0, stream>>>(p);
 }
 
 }  // namespace

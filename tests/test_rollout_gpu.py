@@ -187,3 +187,36 @@ def test_ticketed_rollout_equals_static_rollout():
         assert r.returncode == 0, r.stderr[-2000:]
         res[name] = r.stdout.strip().splitlines()[-1]
     assert res['tickets'] == res['static'] == res['tickets8'], res
+
+
+@pytest.mark.parametrize("game,N", [('Geister', 16384), ('Geister', 1000), ('CIGeister', 77), ('TicTacToe', 4096)])
+def test_bulk_store_rollout_equals_stg_rollout(game, N):
+    """k_rollout<G, TMA>: the staged bulk-store emit path (cp.async.bulk.global.shared::cta) writes the same
+    moments, records, states and counters as the STG.128 path - full tickets, ragged last groups, odd row counts."""
+    import torch
+    from handyrl_b200 import _lib
+    from handyrl_b200.engine import BatchedEnv
+    res = []
+    for knob in (0, 1):
+        _lib.set_tuning('emit_tma', knob)
+        try:
+            env = BatchedEnv(game, N)
+            W = 2 if N % 2 == 0 else 1               # several waves need an even N (16-byte aligned wave bases)
+            main, scalar = env.alloc_obs(waves=W)
+            main.fill_(-7)
+            waves = dict(main=main, scalar=scalar, action_mask=torch.full((W, N, env.A), -7.0, device='cuda'))
+            if scalar is not None:
+                scalar.fill_(-7)
+            act = torch.full((W, N), -9, dtype=torch.int32, device='cuda')
+            traj = torch.zeros(N, 64, 8, dtype=torch.int32, device='cuda')
+            ctr = torch.zeros(8, dtype=torch.int64, device='cuda')
+            for n in (9, 12):
+                env.rollout(n, seed=5, waves=waves, traj=traj, counters=ctr, out_action=act)
+            torch.cuda.synchronize()
+            res.append([t.clone() for t in (main, waves['action_mask'], act, traj, env.state, ctr[:5])] +
+                       ([scalar.clone()] if scalar is not None else []))
+        finally:
+            _lib.set_tuning('emit_tma', None)
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
+    assert float(res[0][0].min()) >= 0            # every byte of the wave buffers was written
