@@ -168,18 +168,63 @@ def cpu_baseline(seconds_target=12.0):
             "phase_share": {"generation": ph[0] / tot, "make_batch": ph[1] / tot, "targets": ph[2] / tot}}
 
 
-def cpu_baseline_reference(seconds=6.0):
+def cpu_baseline_reference(seconds=6.0, parts="generation,generation_net,make_batch,targets"):
     """The UNMODIFIED reference's own Python path (baseline/_ref, installed by tools/install_ref.sh) timed on this
     box's host cores in os.cpu_count() single-threaded processes: Generator.generate (RandomModel and GeisterNet),
     make_batch, losses.compute_target - a separate process so that its torch thread settings and
     forks stay away from this one."""
     try:
         r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "time_reference.py"), "--seconds", str(seconds),
-                            "--parts", "generation,generation_net,make_batch,targets"], stdout=subprocess.PIPE,
+                            "--parts", parts], stdout=subprocess.PIPE,
                            stderr=subprocess.PIPE, timeout=300, text=True)
         return json.loads(r.stdout.strip().splitlines()[-1])
     except Exception as ex:       # reported, never fatal for the GPU numbers
         return {"unavailable": "time_reference.py failed: %r" % (ex,)}
+
+
+def learner_leg(dev, rank, world, barrier):
+    """BASELINE configs[2] and [3]: the actor-learner loop (handyrl_b200/loop.py) with the network in the loop - the
+    only place where this path has collectives: one flat gradient all-reduce per optimiser step and one flat weight
+    broadcast per epoch (NCCL), on the training stream beside the next generation wave.  Reported next to the
+    device-only numbers, never mixed into `value`: >99 % of a ply here is the PyTorch forward (library code)."""
+    import torch
+    import torch.distributed as dist
+    from handyrl_b200.loop import ActorLearner, DEFAULT_ARGS
+    out = {}
+    cases = (("Geister", 16384, 16, "VTRACE", "UPGO", 10, 192), ("ParallelTicTacToe", 65536, 16, "TD", "TD", 10, 32))
+    for env_name, games, plies, vt, pt, epochs, prefill in cases:
+        args = dict(DEFAULT_ARGS, value_target=vt, policy_target=pt, batch_size=256, minimum_episodes=400)
+        al = ActorLearner(env_name, games, args, dev, rank, world, overlap=True)
+        al.gen.rollout(prefill)                      # epoch-0 policy (zero logits) fills the replay before timing
+        al.snap.copy_(al.gen.store.counters)
+        train_steps = 4
+        for _ in range(2):
+            res = al.epoch(plies, train_steps)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(epochs):
+            res = al.epoch(plies, train_steps)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            tt = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt.item())
+        coll = al.collective_times()
+        out[env_name] = {
+            "games_per_gpu": games, "plies_per_epoch": plies, "train_steps_per_epoch": train_steps,
+            "batch": [args["batch_size"], args["forward_steps"]], "value_target": vt, "policy_target": pt,
+            "epochs_timed": epochs, "ms_per_epoch": ms / epochs,
+            "env_steps_per_s": games * plies * world * epochs / (ms * 1e-3),
+            "train_steps_per_s": train_steps * epochs / (ms * 1e-3),
+            "trained": res is not None, "loss_total": (res[0]["total"] if res else None),
+            "net": type(al.net).__name__, "params": sum(p.numel() for p in al.net.parameters()),
+            "collectives": coll, "overlap": "generation stream || training stream (+NCCL)", "ranks": world}
+        del al
+        torch.cuda.empty_cache()
+    return out
 
 
 RESULT_OUT = sys.stdout
@@ -227,6 +272,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-learner", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -550,6 +596,20 @@ def main():
                                 "note": "BatchedEnv.step_observe per ply with pinned-host actions in and fp32 "
                                         "observation/action_mask/reward/terminal out (1.96 kB per env-step over PCIe)"}
 
+    learner = None
+    if not args.no_learner:
+        learner = learner_leg(dev, rank, world, barrier)
+        if world > 1:
+            # the reference's workers with the real net (batch-of-1 CPU forward per ply, worker.py:52, model.py:43-53)
+            # on this box's cores, timed by rank 0 while the other ranks wait
+            if rank == 0:
+                ref = cpu_baseline_reference(5.0, parts="generation_net")
+                learner["reference_workers"] = {
+                    "env_steps_per_s": (ref.get("rates") or {}).get("generation_real_net_env_steps_per_s"),
+                    "cores": ref.get("cores"), "kind": "reference",
+                    "sample": "Generator.generate, Geister, ModelWrapper(GeisterNet), os.cpu_count() processes, 5 s"}
+            dist.barrier()
+
     if rank == 0:
         peak, peak_kind = load_peaks()
 
@@ -586,6 +646,7 @@ def main():
                        "env_steps_per_sec_rollout_only": env_steps_per_step / (roll_ms * 1e-3)},
             "roofline": roofs[dominant], "rooflines": roofs,
             "clocks": clocks, "e2e": e2e, "gpu_launches": 4 * n_timed,
+            "extra": {"learner": learner},
         }
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline()

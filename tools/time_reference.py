@@ -164,6 +164,53 @@ def measure(seconds=6.0, procs=None, parts=('generation', 'make_batch', 'targets
     return out
 
 
+def sweep_targets_cpu(cells=((32, 4096), (200, 4096), (1024, 4096), (32, 65536)), budget=0.4):
+    """BASELINE configs[4] on the host: the reference's losses.compute_target on CPU tensors of tools/sweep_targets.py's
+    cells, with 1 torch thread (what the reference runs with: main.py:10, model.py:8) and with all cores.  Element
+    rates per (T, B, head, mode); B = 65,536 only at T = 32."""
+    sys.path.insert(0, REF)
+    import torch
+    from handyrl.losses import compute_target
+    cores = os.cpu_count() or 1
+    rows = []
+    g = torch.Generator().manual_seed(0)
+    for T, B in cells:
+        P = 2
+        v = torch.tanh(torch.randn(B, T, P, 1, generator=g))
+        rew = torch.full((B, T, P, 1), -0.01)
+        ret = torch.randn(B, T, P, 1, generator=g)
+        oc = torch.randint(-1, 2, (B, 1, P, 1), generator=g).float()
+        rho = torch.exp(0.5 * torch.randn(B, T, 1, 1, generator=g)).clamp(0, 1)
+        c = rho.clone()
+        n = B * T * P
+        for head in ("return", "value"):
+            for mode in ("MC", "TD", "UPGO", "VTRACE", "VTRACE+UPGO"):
+                def call():
+                    for m in (mode.split("+")):
+                        if head == "return":
+                            compute_target(m, v, ret, rew, 0.7, 0.8, rho, c)
+                        else:
+                            compute_target(m, v, oc, None, 0.7, 1.0, rho, c)
+                rates = {}
+                for threads in (1, cores):
+                    torch.set_num_threads(threads)
+                    call()
+                    call()                                  # the first call after a thread-count change builds the pool
+                    k, t0 = 0, time.perf_counter()
+                    while True:
+                        call()
+                        k += 1
+                        dt = time.perf_counter() - t0
+                        if dt >= budget or k >= 50:
+                            break
+                    rates[threads] = n * k / dt
+                rows.append({"T": T, "B": B, "head": head, "mode": mode, "elements_per_s_1_thread": rates[1],
+                             "elements_per_s_all_threads": rates[cores]})
+    return {"cores": cores, "kind": "reference", "rows": rows,
+            "sample": "handyrl.losses.compute_target (baseline/_ref) on CPU tensors, >= %.1f s or 50 calls per cell; "
+                      "VTRACE+UPGO = the two calls of train.py:248-253" % budget}
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--seconds", type=float, default=6.0)
@@ -172,5 +219,9 @@ if __name__ == "__main__":
     ap.add_argument("--env", default="Geister")
     ap.add_argument("--T", type=int, default=32)
     ap.add_argument("--target-rows", type=int, default=1024)
+    ap.add_argument("--sweep-targets", action="store_true")
     a = ap.parse_args()
+    if a.sweep_targets:
+        print(json.dumps(sweep_targets_cpu()))
+        sys.exit(0)
     print(json.dumps(measure(a.seconds, a.procs or None, tuple(a.parts.split(',')), a.env, a.T, a.target_rows)))
