@@ -273,6 +273,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-learner", action="store_true")
+    ap.add_argument("--rounds", type=int, default=0, help="repeat the K timed steps this many times (0: >= 0.35 s)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -364,7 +365,7 @@ def main():
     step(0)
     t_probe1.record()
     torch.cuda.synchronize()
-    rounds = max(1, int(0.35 / (args.steps * t_probe0.elapsed_time(t_probe1) * 1e-3) + 0.999))
+    rounds = args.rounds or max(1, int(0.35 / (args.steps * t_probe0.elapsed_time(t_probe1) * 1e-3) + 0.999))
     if world > 1:
         rr = torch.tensor([rounds], device=dev)
         dist.all_reduce(rr, op=dist.ReduceOp.MAX)
@@ -628,12 +629,19 @@ def main():
                             tgt_ms, BYTES_PER_TARGET_PAIR, "(b,t,p) element, both heads"),
         }
         dominant = max(roofs, key=lambda k: roofs[k]["avg_ms"])
+        # dram bytes per launch from the ncu --set full capture of this workload (tools/measure_round.sh ->
+        # tools/make_traffic.py).  Only valid for the sources it was captured with: a stale file reads as null.
         traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(traffic_file):
             with open(traffic_file) as f:
                 tr = json.load(f)
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            from make_traffic import source_hash
+            fresh = tr.get("_source_hash") == source_hash()
             for k in roofs:
-                roofs[k]["traffic"] = tr.get(k)
+                roofs[k]["traffic"] = tr.get(k) if fresh else None
+                roofs[k]["traffic_source"] = tr.get("_source") if fresh else (
+                    "stale: profiles/traffic.json was captured with other CUDA sources (re-run tools/measure_round.sh)")
         line = {
             "metric": "geister_selfplay_env_steps_per_sec", "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / n_timed,

@@ -1,0 +1,52 @@
+"""What each side output of k_rollout costs on the bench workload (65,536 Geister games x 32 plies per launch):
+full = moments + action + trajectory records + episode table; then without the record ring, without the episode
+table, with the static schedule (knob rollout_chunk = 0), with bulk-store emit (knob emit_tma = 1).
+    python tools/probe_rollout_parts.py"""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from handyrl_b200 import _lib  # noqa: E402
+from handyrl_b200.engine import BatchedEnv  # noqa: E402
+
+N, PLIES, D = 65536, 32, 512
+
+
+def run(name, traj=True, table=True, knobs=()):
+    for k, v in knobs:
+        _lib.set_tuning(k, v)
+    env = BatchedEnv("Geister", N)
+    main, scalar = env.alloc_obs(waves=2)
+    waves = dict(main=main, scalar=scalar, action_mask=torch.empty(2, N, env.A, device="cuda"))
+    act = torch.empty(2, N, dtype=torch.int32, device="cuda")
+    tr = torch.zeros(N, D, 8, dtype=torch.int32, device="cuda") if traj else None
+    ept = torch.zeros(1 << 20, 4, dtype=torch.int32, device="cuda") if table else None
+    ctr = torch.zeros(8, dtype=torch.int64, device="cuda")
+    for _ in range(10):
+        env.rollout(PLIES, seed=1, waves=waves, traj=tr, ep_table=ept, counters=ctr, out_action=act)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    K = 200
+    for _ in range(K):
+        env.rollout(PLIES, seed=1, waves=waves, traj=tr, ep_table=ept, counters=ctr, out_action=act)
+    e1.record()
+    torch.cuda.synchronize()
+    for k, _ in knobs:
+        _lib.set_tuning(k, None)
+    ms = e0.elapsed_time(e1) / K
+    byt = N * PLIES * (1940 + (32 if traj else 0))
+    return {"case": name, "ms": round(ms, 4), "TBps": round(byt / ms / 1e9, 3)}
+
+
+if __name__ == "__main__":
+    rows = [run("full"), run("no trajectory ring", traj=False), run("no episode table", table=False),
+            run("no ring, no table", traj=False, table=False),
+            run("static schedule", knobs=(("rollout_chunk", 0),)), run("bulk-store emit", knobs=(("emit_tma", 1),)),
+            run("full (again)")]
+    for r in rows:
+        print(r, file=sys.stderr)
+    print(json.dumps(rows))
