@@ -203,6 +203,16 @@ def allreduce_gradients(params, group=None, extra=None):
     return bucket[off:].tolist() if extra is not None else None
 
 
+def all_ranks_have(count, minimum, group=None):
+    """True iff EVERY rank's `count` (a 1-element tensor or a number) reaches `minimum` - the collective form of the
+    trainer's `len(episodes) < minimum_episodes` gate (train.py:330-331).  Every rank gets the same answer, so all of
+    them enter (or skip) the same sequence of NCCL calls afterwards."""
+    n = count.detach().clone().reshape(1) if torch.is_tensor(count) else torch.tensor([int(count)], dtype=torch.int64)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(n, op=dist.ReduceOp.MIN, group=group)
+    return int(n.item()) >= int(minimum)
+
+
 def broadcast_weights(model, src=0, group=None):
     """Parameters and buffers (BatchNorm statistics) from rank `src` to every rank as one flat broadcast."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:

@@ -20,7 +20,7 @@ import torch.distributed as dist
 
 from . import nets
 from .generation import BatchGenerator
-from .learner import DataParallelLearner, broadcast_weights
+from .learner import DataParallelLearner, all_ranks_have, broadcast_weights
 from .train import make_batch_windows
 
 DEFAULT_ARGS = {  # reference config.yaml train_args
@@ -111,10 +111,7 @@ class ActorLearner:
     def _ready(self):
         """train.py:330-331: no training before `minimum_episodes` - decided COLLECTIVELY (every rank must enter the
         same sequence of NCCL calls): the minimum over the ranks of the episodes usable by the trainer."""
-        n = self.snap[0:1].clone()
-        if self.world > 1:
-            dist.all_reduce(n, op=dist.ReduceOp.MIN)
-        return int(n.item()) >= self.args['minimum_episodes']
+        return all_ranks_have(self.snap[0:1], self.args['minimum_episodes'])
 
     def epoch(self, plies, train_steps):
         """generation wave e  ||  training on the episodes of waves < e;  then weights: rank 0 -> all ranks -> actor"""

@@ -81,7 +81,7 @@ def _free_port():
 def _dp_worker(rank, world, port, q):
     import torch.distributed as dist
     from handyrl_b200 import nets
-    from handyrl_b200.learner import allreduce_gradients, broadcast_weights
+    from handyrl_b200.learner import all_ranks_have, allreduce_gradients, broadcast_weights
     dist.init_process_group('gloo', init_method='tcp://127.0.0.1:%d' % port, rank=rank, world_size=world)
     torch.manual_seed(100 + rank)                       # ranks start from different weights
     net = nets.SimpleConv2dModel()
@@ -102,6 +102,8 @@ def _dp_worker(rank, world, port, q):
         gs = [torch.zeros_like(g) for _ in range(world)]
         dist.all_gather(gs, g)
         ok = ok and torch.allclose(p.grad, sum(gs) / world, rtol=1e-6, atol=1e-7)
+    # the minimum_episodes gate is collective: rank 1 has too few episodes -> nobody trains (loop.py)
+    ok = ok and all_ranks_have(500, 400) and not all_ranks_have(torch.tensor([500 if rank == 0 else 10]), 400)
     q.put((rank, same_weights, ok))
     dist.destroy_process_group()
 
