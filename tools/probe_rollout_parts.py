@@ -46,6 +46,9 @@ if __name__ == "__main__":
     rows = [run("full"), run("no trajectory ring", traj=False), run("no episode table", table=False),
             run("no ring, no table", traj=False, table=False),
             run("static schedule", knobs=(("rollout_chunk", 0),)), run("bulk-store emit", knobs=(("emit_tma", 1),)),
+            run("tickets of 8 plies", knobs=(("rollout_chunk", 8),)),
+            run("tickets of 16 plies", knobs=(("rollout_chunk", 16),)),
+            run("tickets of 8 plies, no ring", traj=False, knobs=(("rollout_chunk", 8),)),
             run("full (again)")]
     for r in rows:
         print(r, file=sys.stderr)
