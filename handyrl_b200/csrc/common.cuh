@@ -73,9 +73,26 @@ __device__ __forceinline__ uint64_t ring_mod(uint64_t x, uint64_t m) {
     return (m & (m - 1)) == 0 ? (x & (m - 1)) : (x % m);
 }
 
+// Ring address of the record of (iteration it, game slot i), in 32-byte records.
+//   B200RL_RING_TILE == 0: slot-major [N][D] - the D plies of a slot are contiguous (a training window = T x 32 B).
+//   B200RL_RING_TILE == TP: tiled [N/32][D/TP][32 games][TP plies] - a warp's 32 games x TP plies are one
+//       contiguous 32 x TP x 32 B block, a window is T/TP pieces of TP x 32 B (N padded to 32, D % TP == 0).
+#ifndef B200RL_RING_TILE
+#define B200RL_RING_TILE 0
+#endif
+__device__ __forceinline__ int64_t ring_index(int64_t D, uint64_t it, int64_t i) {
+    const int64_t r = (int64_t)ring_mod(it, (uint64_t)D);
+#if B200RL_RING_TILE == 0
+    return i * D + r;
+#else
+    constexpr int64_t TP = B200RL_RING_TILE;
+    return (((i >> 5) * (D / TP) + r / TP) * 32 + (i & 31)) * TP + (r % TP);
+#endif
+}
+
 __device__ __forceinline__ void st_record(void* traj, int64_t D, int64_t N, uint64_t it, int64_t i,
                                           const uint32_t (&r)[8]) {
-    uint32_t* p = reinterpret_cast<uint32_t*>(traj) + (i * D + (int64_t)ring_mod(it, (uint64_t)D)) * 8;
+    uint32_t* p = reinterpret_cast<uint32_t*>(traj) + ring_index(D, it, i) * 8;
     asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]),
                  "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
                  : "memory");
@@ -83,7 +100,7 @@ __device__ __forceinline__ void st_record(void* traj, int64_t D, int64_t N, uint
 
 __device__ __forceinline__ void ld_record(const void* traj, int64_t D, int64_t N, uint64_t it, int64_t i,
                                           uint32_t (&r)[8]) {
-    const uint32_t* p = reinterpret_cast<const uint32_t*>(traj) + (i * D + (int64_t)ring_mod(it, (uint64_t)D)) * 8;
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(traj) + ring_index(D, it, i) * 8;
     asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "l"(p));

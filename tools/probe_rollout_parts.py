@@ -15,7 +15,7 @@ from handyrl_b200.engine import BatchedEnv  # noqa: E402
 N, PLIES, D = 65536, 32, 512
 
 
-def run(name, traj=True, table=True, knobs=()):
+def run(name, traj=True, table=True, knobs=(), D=D):
     for k, v in knobs:
         _lib.set_tuning(k, v)
     env = BatchedEnv("Geister", N)
@@ -49,6 +49,13 @@ if __name__ == "__main__":
             run("tickets of 8 plies", knobs=(("rollout_chunk", 8),)),
             run("tickets of 16 plies", knobs=(("rollout_chunk", 16),)),
             run("tickets of 8 plies, no ring", traj=False, knobs=(("rollout_chunk", 8),)),
+            # ring depth: 512 makes the slot stride a power of two (16 KB): every game's record line of a ply group
+            # has the same low 14 address bits
+            run("ring depth 516", D=516), run("ring depth 520", D=520), run("ring depth 544", D=544),
+            run("ring depth 772", D=772),
+            # tiny rings: the same instructions, but the 32 lines a warp flushes are (nearly) contiguous
+            run("ring depth 4 (4 KB contiguous per warp flush)", D=4), run("ring depth 8", D=8),
+            run("ring depth 32", D=32), run("ring depth 128", D=128),
             run("full (again)")]
     for r in rows:
         print(r, file=sys.stderr)
