@@ -406,7 +406,7 @@ def main():
         st = gen.store
         torch.cuda.synchronize()
         # slab of 65,536 rows per read-back: a rollout finishes ~13,400 episodes and commits lag up to two steps
-        index = HostReplayIndex(gen, max_new_rows=1 << 16, n_threads=max(1, min(8, (os.cpu_count() or 1) // world - 1)),
+        index = HostReplayIndex(gen, max_new_rows=1 << 16, n_threads=max(1, min(8, (os.cpu_count() or 1) // world)),
                                 slots=4)
         DEPTH = 3                                            # window / summary slots in flight
         LOOK = 2                                             # windows of step k are drawn after rollout k-2
@@ -494,9 +494,11 @@ def main():
                 ev_tail[s].record()
                 with torch.cuda.stream(sum_stream):                             # result of the step -> host
                     sum_stream.wait_event(ev_tail[s])
-                    for t_ in (tv, av, tr, ar):
-                        t_.record_stream(sum_stream)
-                    met_pin[s].copy_(torch.stack([tv.mean(), av.mean(), tr.mean(), ar.mean()]), non_blocking=True)
+                    # the four outputs are views of ONE (2, 2, B, T, P, 1) buffer (compute_target_heads): one reduction
+                    base = tv._base if (tv._base is not None and tv._base.numel() == 4 * tv.numel()) else \
+                        torch.stack([tv, av, tr, ar])
+                    base.record_stream(sum_stream)
+                    met_pin[s].copy_(base.view(4, -1).mean(dim=1), non_blocking=True)
                     ev_done[s].record()
                 evk[5].record()
             t_d = pc()
