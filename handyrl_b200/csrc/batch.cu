@@ -523,8 +523,9 @@ __host__ __device__ inline void select_one_window(const int32_t* ep_table, int64
     uint64_t end_it = 0, c = draw0;
     const bool e_pow2 = (E & (E - 1)) == 0;
     for (int tr = 0; tr < 64; ++tr) {
-        c = draw0 + 4ull * (uint64_t)tr;
-        const uint32_t r0 = b200rl_rand32(seed, (uint64_t)b, c), r1 = b200rl_rand32(seed, (uint64_t)b, c + 1);
+        c = draw0 + 2ull * (uint64_t)tr;
+        const uint64_t x = b200rl_rand64(seed, (uint64_t)b, c);   // one hash per try: index draw | acceptance draw
+        const uint32_t r0 = (uint32_t)(x >> 32), r1 = (uint32_t)x;
         int64_t ep_idx = (int64_t)(((unsigned long long)r0 * (unsigned long long)n_draw) >> 32);  // train.py:286
         const double accept = 1.0 - (double)(L - 1 - ep_idx) / (double)maximum_episodes;         // train.py:287
         const bool last_try = tr == 63;
@@ -542,7 +543,8 @@ __host__ __device__ inline void select_one_window(const int32_t* ep_table, int64
         if (last_try || alive) break;
     }
     // the window-start and solo-player draws of the accepted try (rejected tries never needed theirs)
-    const uint32_t r2 = b200rl_rand32(seed, (uint64_t)b, c + 2), r3 = b200rl_rand32(seed, (uint64_t)b, c + 3);
+    const uint64_t y = b200rl_rand64(seed, (uint64_t)b, c + 1);
+    const uint32_t r2 = (uint32_t)(y >> 32), r3 = (uint32_t)y;
     const int cand = 1 + (steps - forward_steps > 0 ? steps - forward_steps : 0);         // train.py:291
     const int st = (int)(((unsigned long long)r2 * (unsigned long long)cand) >> 32);       // train.py:292
     const int ed = st + forward_steps < steps ? st + forward_steps : steps;               // train.py:293
@@ -761,32 +763,13 @@ extern "C" int b200rl_select_windows_host(const int32_t* ep_table_host, int64_t 
                    "select_windows_host: bad E/D/maximum_episodes/forward_steps/B");
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 64) n_threads = 64;
-    // The table (16 B per finished episode, up to E rows) does not fit the host caches and an accepted try reads
-    // one random row: that row is prefetched for the next PF windows while the current block is drawn (the draws
-    // are counter-based, so they can be recomputed).
-    int64_t Lh = (int64_t)(cursor < (unsigned long long)E ? cursor : (unsigned long long)E);
-    if (Lh > maximum_episodes) Lh = maximum_episodes;
-    auto prefetch = [&](int64_t b) {   // the row of the first try the recency law accepts (almost always the one used)
-        if (Lh <= 0) return;
-        for (int tr = 0; tr < 8; ++tr) {
-            const uint64_t c = draw0 + 4ull * (uint64_t)tr;
-            const uint32_t r0 = b200rl_rand32(seed, (uint64_t)b, c), r1 = b200rl_rand32(seed, (uint64_t)b, c + 1);
-            const int64_t ep_idx = (int64_t)(((unsigned long long)r0 * (unsigned long long)Lh) >> 32);
-            const double accept = 1.0 - (double)(Lh - 1 - ep_idx) / (double)maximum_episodes;
-            if (!((double)r1 * (1.0 / 4294967296.0) < accept)) continue;
-            const unsigned long long pos = cursor - (unsigned long long)Lh + (unsigned long long)ep_idx;
-            __builtin_prefetch(ep_table_host + (int64_t)(pos % (unsigned long long)E) * 4);
-            return;
-        }
-    };
-    constexpr int64_t PF = 16;
+    // The rows a call draws from are the newest min(cursor, E, maximum_episodes) x 16 B (1.6 MB at the reference's
+    // maximum_episodes): they sit in the host's L2/L3, and a try rejected by the recency law never touches its row, so
+    // r1's software prefetch (which recomputed the draws of the next windows) cost more hashing than it saved.
     auto work = [&](int64_t lo, int64_t hi) {
-        for (int64_t b = lo; b < hi && b < lo + PF; ++b) prefetch(b);
-        for (int64_t b = lo; b < hi; ++b) {
-            if (b + PF < hi) prefetch(b + PF);
+        for (int64_t b = lo; b < hi; ++b)
             select_one_window(ep_table_host, E, cursor, maximum_episodes, (int)forward_steps, seed, draw0, it_now, D, b,
                               out_windows_host + b * 8);
-        }
     };
     if (n_threads == 1 || B < 4096) {
         work(0, B);

@@ -116,6 +116,11 @@ __host__ __device__ __forceinline__ uint64_t b200rl_mix64(uint64_t z) {
     return z ^ (z >> 31);
 }
 
+// 64 random bits per (seed, stream, counter): window selection takes two 32-bit draws from each
+__host__ __device__ __forceinline__ uint64_t b200rl_rand64(uint64_t seed, uint64_t stream, uint64_t counter) {
+    return b200rl_mix64(seed ^ b200rl_mix64(stream * 0xD6E8FEB86659FD93ull + counter));
+}
+
 __host__ __device__ __forceinline__ uint32_t b200rl_rand32(uint64_t seed, uint64_t stream, uint64_t counter) {
     uint64_t h = b200rl_mix64(seed ^ b200rl_mix64(stream * 0xD6E8FEB86659FD93ull + counter));
     return (uint32_t)(h >> 32);

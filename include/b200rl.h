@@ -277,7 +277,7 @@ int b200rl_make_batch(int game, const void* traj, int64_t D, int64_t N, const fl
  * Batcher.select_episode (handyrl/train.py:284-302) for B windows: recency-biased rejection sampling
  * over the last min(finished, E, maximum_episodes) rows of the finished-episode table (index 0 =
  * oldest), then a uniform window start.  Rows whose first ply left the trajectory ring (older than D
- * iterations before it_now) are rejected.  Draws: counter RNG keyed (seed, b, draw0 + 4*try + j).
+ * iterations before it_now) are rejected.  Draws: counter RNG keyed (seed, b, draw0 + 2*try + j), two 32-bit draws per 64-bit hash.
  *   out_windows (B,8) int32 in the layout b200rl_make_batch consumes (solo player = 1 random bit).
  * Reads counters[5] on the device: no host synchronisation between rollout and window selection.
  */

@@ -18,8 +18,12 @@ def mix64(z):
     return z ^ (z >> 31)
 
 
+def rand64(seed, stream, counter):
+    return mix64(seed ^ mix64((stream * 0xD6E8FEB86659FD93 + counter) & M64))
+
+
 def rand32(seed, stream, counter):
-    return mix64(seed ^ mix64((stream * 0xD6E8FEB86659FD93 + counter) & M64)) >> 32
+    return rand64(seed, stream, counter) >> 32
 
 
 def select_windows(ep_table, cursor, maximum_episodes, forward_steps, seed, draw0, it_now, D, B):
@@ -33,8 +37,9 @@ def select_windows(ep_table, cursor, maximum_episodes, forward_steps, seed, draw
             continue
         n_draw = min(L, maximum_episodes)
         for tr in range(64):
-            c = draw0 + 4 * tr
-            r0, r1, r2, r3 = (rand32(seed, b, c + j) for j in range(4))
+            c = draw0 + 2 * tr                       # one 64-bit hash per try: index draw | acceptance draw
+            x, y = rand64(seed, b, c), rand64(seed, b, c + 1)
+            r0, r1, r2, r3 = x >> 32, x & 0xFFFFFFFF, y >> 32, y & 0xFFFFFFFF
             ep_idx = (r0 * n_draw) >> 32                                   # train.py:286
             accept = 1.0 - (L - 1 - ep_idx) / maximum_episodes              # train.py:287
             last_try = tr == 63
