@@ -11,6 +11,7 @@ import hashlib
 import io
 import json
 import os
+import re
 import subprocess
 import sys
 
@@ -43,8 +44,9 @@ def main(rep, out):
     for phase, keys in PHASES.items():
         tot, found = 0.0, []
         for name, v in per.items():
-            base = name.split("<")[0].split("(")[0].split("::")[-1].strip()
-            if base in keys:
+            # ncu prints e.g. "void <unnamed>::k_rollout<GeisterGame<0>, 0>(<unnamed>::RolloutParams)"
+            m = re.search(r"\b(k_[A-Za-z0-9_]+)", name)
+            if m and m.group(1) in keys:
                 tot += sum(v) / len(v)
                 found.append(name[:100])
         if not found:
