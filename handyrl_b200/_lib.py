@@ -67,6 +67,8 @@ SIGNATURES = {
     "b200rl_env_rollout": [c_int, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
                            c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr],
     "b200rl_env_rollout_scratch_bytes": [c_i64],
+    "b200rl_env_rollout_static": [c_int, c_ptr, c_i64, c_i64, c_u64, c_u64, c_u64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
+                                  c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr],
     "b200rl_set_tuning": [ctypes.c_char_p, c_i64, c_int],
     "b200rl_env_step_record": [c_int, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_int, c_ptr, c_i64, c_u64, c_ptr, c_i64,
                                c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],

@@ -724,3 +724,44 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     DISPATCH_GAME(game, launch_rollout<G>(p, want, dev, sms, (cudaStream_t)stream));
     return b200rl_check_launch("k_rollout");
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// b200rl_env_rollout_static: b200rl_env_rollout for callers that cannot allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The ticket scratch of k_rollout lives in a file-scope __device__ array of a stated maximum size instead
+// of a caller buffer: every GPU that loads the library holds these B200RL_ROLLOUT_STATIC_MAX_GAMES / 32 + 32 words
+// (32,896 bytes) until the process exits.
+//
+// In HOST code `g_rollout_static_sched` is only a stand-in for the symbol, not a device address: its device address is
+// asked for once per device, with that device current (cudaGetSymbolAddress), and that pointer is what the kernel gets.
+// All calls on a device share the array.  It keeps the previous call's contents; the launcher clears the words a
+// launch uses on the caller's stream (cudaMemsetAsync) before the kernel, so calls on ONE stream are safe back to
+// back, while calls that overlap on the GPU (different streams, concurrent graphs) race on the ticket counters.
+// ---------------------------------------------------------------------------------------------------------------
+static_assert(B200RL_ROLLOUT_STATIC_MAX_GAMES % 32 == 0, "whole groups of 32 games");
+static __device__ __align__(256) unsigned int g_rollout_static_sched[SCHED_HDR + B200RL_ROLLOUT_STATIC_MAX_GAMES / 32];
+
+extern "C" int b200rl_env_rollout_static(int game, void* state, int64_t N, int64_t n_plies, uint64_t seed,
+                                         uint64_t game_id_base, uint64_t it0, float* out_main, float* out_scalar,
+                                         float* out_amask, int32_t* out_action, int64_t waves, void* traj, int64_t D,
+                                         int32_t* ep_table, int64_t E, uint64_t* counters, void* stream) {
+    B200RL_REQUIRE(N <= (int64_t)B200RL_ROLLOUT_STATIC_MAX_GAMES,
+                   "env_rollout_static: N = %lld games exceeds the static scratch (B200RL_ROLLOUT_STATIC_MAX_GAMES = %d); "
+                   "use b200rl_env_rollout with a caller-owned scratch buffer",
+                   (long long)N, (int)B200RL_ROLLOUT_STATIC_MAX_GAMES);
+    static std::atomic<unsigned int*> sched_of_dev[64];   // device address of the array, per device
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    B200RL_REQUIRE(e == cudaSuccess && dev >= 0 && dev < 64, "env_rollout_static: cudaGetDevice: %s (device %d)",
+                   cudaGetErrorString(e), dev);
+    unsigned int* sched = sched_of_dev[dev].load(std::memory_order_acquire);
+    if (sched == nullptr) {   // set-up, once per device, with that device current (a race here is benign: same answer)
+        e = cudaGetSymbolAddress((void**)&sched, g_rollout_static_sched);
+        B200RL_REQUIRE(e == cudaSuccess && sched != nullptr, "env_rollout_static: cudaGetSymbolAddress: %s",
+                       cudaGetErrorString(e));
+        sched_of_dev[dev].store(sched, std::memory_order_release);
+    }
+    return b200rl_env_rollout(game, state, N, n_plies, seed, game_id_base, it0, out_main, out_scalar, out_amask,
+                              out_action, waves, traj, D, ep_table, E, counters, sched,
+                              (int64_t)sizeof(unsigned int) * (SCHED_HDR + B200RL_ROLLOUT_STATIC_MAX_GAMES / 32), stream);
+}

@@ -197,6 +197,24 @@ int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_plies, uint64
 /* Bytes of ticket scratch b200rl_env_rollout needs for N games (-1 for N < 0). */
 int64_t b200rl_env_rollout_scratch_bytes(int64_t N);
 
+/*
+ * b200rl_env_rollout without any allocation on either side of the ABI.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments and results as b200rl_env_rollout minus the scratch: the
+ * ticket counters live in a file-scope `static __device__` array of the library, sized for at most
+ * B200RL_ROLLOUT_STATIC_MAX_GAMES games (32,896 bytes, held by every GPU that loads the library until the process
+ * exits).  N beyond that maximum is rejected with B200RL_ERR_ARG and a message; the call performs no cudaMalloc,
+ * cudaFree or other allocating routine (it resolves the array's device address once per device with
+ * cudaGetSymbolAddress and clears the words it uses with cudaMemsetAsync on `stream`).
+ * All calls on a device SHARE the array: calls issued on one stream are safe back to back, calls that overlap on the
+ * GPU (different streams, concurrent graph launches) race on the ticket counters and must not be made.
+ */
+#define B200RL_ROLLOUT_STATIC_MAX_GAMES 262144
+int b200rl_env_rollout_static(int game, void* state, int64_t N, int64_t n_plies, uint64_t seed, uint64_t game_id_base,
+                              uint64_t it0, float* out_main, float* out_scalar, float* out_amask, int32_t* out_action,
+                              int64_t waves, void* traj, int64_t D, int32_t* ep_table, int64_t E, uint64_t* counters,
+                              void* stream);
+
 /* ------------------------------------------------------------------ */
 /* Part 2: episode -> batch assembly — handyrl/train.py:33-133          */
 /* ------------------------------------------------------------------ */
