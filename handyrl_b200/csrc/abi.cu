@@ -36,6 +36,7 @@ Knob g_knobs[B200RL_TUNE_COUNT] = {
     {"target_no_dual", "B200RL_TARGET_NO_DUAL", {0}, {0}},
     {"target_persistent", "B200RL_TARGET_PERSISTENT", {0}, {0}},
     {"emit_tma", "B200RL_EMIT_TMA", {0}, {0}},
+    {"target_ws_rowlane", "B200RL_TARGET_WS_ROWLANE", {0}, {0}},
 };
 }  // namespace
 

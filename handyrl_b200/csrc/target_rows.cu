@@ -180,6 +180,82 @@ __device__ __forceinline__ void scan_group(const float (&v)[4 * P], const float 
     }
 }
 
+// One chunk of `tl` timesteps (a multiple of 4, descending) of ONE batch row held by this lane, all P players: the
+// row's slivers sit in shared memory at pv (values -> advantages), pr (rewards -> targets), prho / pc.  Every
+// LDS.128 / STS.128 carries 4 useful floats (2 timesteps x 2 players at P = 2), and the P independent sequences of
+// the row interleave in the fp32 pipe.  Software pipeline over the 4-timestep groups with two register sets
+// (ping-pong): the LDS.128 of group q-1 are issued before the dependent chain of group q, and no register is copied
+// between iterations.  `first_chunk`: the chunk starts with the bootstrap step t = T-1, whose group is peeled off.
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
+__device__ __forceinline__ void scan_chunk_rowlane(float* pv, float* pr, const float* prho, const float* pc,
+                                                   bool c_alias, bool rew_rt, int tl, bool first_chunk,
+                                                   Rec<MT> (&rec_t)[P], Rec<MA> (&rec_a)[P], const float (&R)[P],
+                                                   const ScanParams& k) {
+    constexpr int WR = RHO_PP ? P : 1;
+    struct Grp { float4 v[P], r[P], rho[WR], c[WR]; };
+    auto load_group = [&](Grp& g, int q) {
+#pragma unroll
+        for (int u = 0; u < P; ++u) {
+            g.v[u] = *reinterpret_cast<const float4*>(pv + q * 4 * P + 4 * u);
+            if (HAS_REW) {
+                if (rew_rt) g.r[u] = *reinterpret_cast<const float4*>(pr + q * 4 * P + 4 * u);
+                else g.r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        if (NEED_RHO) {
+#pragma unroll
+            for (int u = 0; u < WR; ++u) {
+                g.rho[u] = *reinterpret_cast<const float4*>(prho + q * 4 * WR + 4 * u);
+                if (!c_alias) g.c[u] = *reinterpret_cast<const float4*>(pc + q * 4 * WR + 4 * u);
+            }
+        }
+    };
+    auto compute_group = [&](const Grp& g, int q, auto first_tag) {
+        constexpr bool FIRST = decltype(first_tag)::value;
+        float v[4 * P], rw[4 * P], rho[4 * WR], cc[4 * WR];
+#pragma unroll
+        for (int u = 0; u < P; ++u) {
+            v[4 * u] = g.v[u].x; v[4 * u + 1] = g.v[u].y; v[4 * u + 2] = g.v[u].z; v[4 * u + 3] = g.v[u].w;
+            if (HAS_REW) {
+                rw[4 * u] = g.r[u].x; rw[4 * u + 1] = g.r[u].y; rw[4 * u + 2] = g.r[u].z; rw[4 * u + 3] = g.r[u].w;
+            }
+        }
+        if (NEED_RHO) {
+#pragma unroll
+            for (int u = 0; u < WR; ++u) {
+                rho[4 * u] = g.rho[u].x; rho[4 * u + 1] = g.rho[u].y; rho[4 * u + 2] = g.rho[u].z; rho[4 * u + 3] = g.rho[u].w;
+                const float4 c4 = c_alias ? g.rho[u] : g.c[u];
+                cc[4 * u] = c4.x; cc[4 * u + 1] = c4.y; cc[4 * u + 2] = c4.z; cc[4 * u + 3] = c4.w;
+            }
+        }
+        float tg[4 * P], ad[4 * P];
+        scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, FIRST>(v, rw, rho, cc, rec_t, rec_a, R, k, tg, ad);
+#pragma unroll
+        for (int u = 0; u < P; ++u) {
+            *reinterpret_cast<float4*>(pv + q * 4 * P + 4 * u) =
+                make_float4(ad[4 * u], ad[4 * u + 1], ad[4 * u + 2], ad[4 * u + 3]);
+            *reinterpret_cast<float4*>(pr + q * 4 * P + 4 * u) =
+                make_float4(tg[4 * u], tg[4 * u + 1], tg[4 * u + 2], tg[4 * u + 3]);
+        }
+    };
+    Grp ga, gb;
+    int q = (tl >> 2) - 1;
+    load_group(ga, q);
+    if (first_chunk) {   // warp-uniform
+        if (q >= 1) load_group(gb, q - 1);
+        compute_group(ga, q, std::true_type{});
+        --q;
+        if (q >= 0) ga = gb;
+    }
+    for (; q >= 1; q -= 2) {
+        load_group(gb, q - 1);
+        compute_group(ga, q, std::false_type{});
+        if (q >= 2) load_group(ga, q - 2);
+        compute_group(gb, q - 1, std::false_type{});
+    }
+    if (q == 0) compute_group(ga, 0, std::false_type{});
+}
+
 // ns = ring depth (2..4 stages): 2 when the grid fills the SMs (more resident warps hide the latency better than
 // deeper rings), up to 4 when there are few tiles and each warp has to cover the DRAM latency on its own.
 // DUAL: the tile belongs to one of two heads launched together (k_target_rows2); whether that head has rewards
@@ -253,71 +329,8 @@ __device__ __forceinline__ void target_rows_tiles(const ScanParams& k, int tile0
                 float* pr = st + TR * RSV + lane * RSV;
                 const float* prho = st + 2 * TR * RSV + lane * RSR;
                 const float* pc = c_alias ? prho : prho + TR * RSR;
-                // Software pipeline over the 4-timestep groups with two register sets (ping-pong): the LDS.128 of
-                // group q-1 are issued before the dependent fp32 chain of group q, and no register is copied
-                // between iterations.  The group holding the bootstrap step t = T-1 is peeled off.
-                struct Grp { float4 v[P], r[P], rho[WR], c[WR]; };
-                auto load_group = [&](Grp& g, int q) {
-#pragma unroll
-                    for (int u = 0; u < P; ++u) {
-                        g.v[u] = *reinterpret_cast<const float4*>(pv + q * 4 * P + 4 * u);
-                        if (HAS_REW) {
-                            if (rew_rt) g.r[u] = *reinterpret_cast<const float4*>(pr + q * 4 * P + 4 * u);
-                            else g.r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        }
-                    }
-                    if (NEED_RHO) {
-#pragma unroll
-                        for (int u = 0; u < WR; ++u) {
-                            g.rho[u] = *reinterpret_cast<const float4*>(prho + q * 4 * WR + 4 * u);
-                            if (!c_alias) g.c[u] = *reinterpret_cast<const float4*>(pc + q * 4 * WR + 4 * u);
-                        }
-                    }
-                };
-                auto compute_group = [&](const Grp& g, int q, auto first_tag) {
-                    constexpr bool FIRST = decltype(first_tag)::value;
-                    float v[4 * P], rw[4 * P], rho[4 * WR], cc[4 * WR];
-#pragma unroll
-                    for (int u = 0; u < P; ++u) {
-                        v[4 * u] = g.v[u].x; v[4 * u + 1] = g.v[u].y; v[4 * u + 2] = g.v[u].z; v[4 * u + 3] = g.v[u].w;
-                        if (HAS_REW) {
-                            rw[4 * u] = g.r[u].x; rw[4 * u + 1] = g.r[u].y; rw[4 * u + 2] = g.r[u].z; rw[4 * u + 3] = g.r[u].w;
-                        }
-                    }
-                    if (NEED_RHO) {
-#pragma unroll
-                        for (int u = 0; u < WR; ++u) {
-                            rho[4 * u] = g.rho[u].x; rho[4 * u + 1] = g.rho[u].y; rho[4 * u + 2] = g.rho[u].z; rho[4 * u + 3] = g.rho[u].w;
-                            const float4 c4 = c_alias ? g.rho[u] : g.c[u];
-                            cc[4 * u] = c4.x; cc[4 * u + 1] = c4.y; cc[4 * u + 2] = c4.z; cc[4 * u + 3] = c4.w;
-                        }
-                    }
-                    float tg[4 * P], ad[4 * P];
-                    scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, FIRST>(v, rw, rho, cc, rec_t, rec_a, R, k, tg, ad);
-#pragma unroll
-                    for (int u = 0; u < P; ++u) {
-                        *reinterpret_cast<float4*>(pv + q * 4 * P + 4 * u) =
-                            make_float4(ad[4 * u], ad[4 * u + 1], ad[4 * u + 2], ad[4 * u + 3]);
-                        *reinterpret_cast<float4*>(pr + q * 4 * P + 4 * u) =
-                            make_float4(tg[4 * u], tg[4 * u + 1], tg[4 * u + 2], tg[4 * u + 3]);
-                    }
-                };
-                Grp ga, gb;
-                int q = (tl >> 2) - 1;
-                load_group(ga, q);
-                if (ch == nchunks - 1) {   // warp-uniform: this chunk starts with the bootstrap step
-                    if (q >= 1) load_group(gb, q - 1);
-                    compute_group(ga, q, std::true_type{});
-                    --q;
-                    if (q >= 0) ga = gb;
-                }
-                for (; q >= 1; q -= 2) {
-                    load_group(gb, q - 1);
-                    compute_group(ga, q, std::false_type{});
-                    if (q >= 2) load_group(ga, q - 2);
-                    compute_group(gb, q - 1, std::false_type{});
-                }
-                if (q == 0) compute_group(ga, 0, std::false_type{});
+                scan_chunk_rowlane<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP>(pv, pr, prho, pc, c_alias != 0, rew_rt, tl,
+                                                                         ch == nchunks - 1, rec_t, rec_a, R, k);
             }
             __syncwarp();
             if (tl == RTC) {
@@ -391,10 +404,16 @@ constexpr int WS_MAX_STAGES = 8;
 constexpr size_t WS_SMEM_CAP = 227 * 1024;             // opt-in dynamic shared memory per CTA on sm_100
 constexpr int WS_BAR_FLOATS = 3 * WS_MAX_STAGES * 2;   // 3 x 8 mbarriers of 8 bytes, in floats
 
-template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC>
+// ROWLANE: the compute warp's lane owns a whole ROW (all P players) instead of one (row, player) sequence, tiles are
+// 32 rows.  Why (profiles/r2_target_ws_rowlane.md): with one sequence per lane the compute warp, which is the critical
+// path at small B, spends 44 cycles per timestep on 12.5 instructions - four of them scalar LDS / STS that cost 3-4
+// issue cycles each, the rest stalled on the 4-deep dependent fp32 chain.  Row per lane, every LDS.128 / STS.128
+// carries 2 timesteps x 2 players (4x fewer shared-memory instructions per sequence) and the second player's chain
+// fills the issue slots the first one leaves empty.
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC, bool ROWLANE>
 __global__ void __launch_bounds__(96) k_target_rows_ws(const ScanParams k, int c_alias, int ns) {
     extern __shared__ __align__(16) float smem[];
-    constexpr int TR = 32 / P;                       // rows per tile: one lane per (row, player)
+    constexpr int TR = ROWLANE ? 32 : 32 / P;        // rows per tile: one lane per row / per (row, player)
     constexpr int RSV = RTC * P + 4;
     constexpr int WR = RHO_PP ? P : 1;
     constexpr int RSR = RTC * WR + 4;
@@ -474,6 +493,34 @@ __global__ void __launch_bounds__(96) k_target_rows_ws(const ScanParams k, int c
                 flush_tile<P, RSV>(st, k.out_a, row_out, b0, rows, t0, tl, lane);
             }
             mbar_arrive(empty + slot);   // in program order after the stores, which consumed this lane's LDS data
+            if (++slot == ns) {
+                slot = 0;
+                par ^= 1;
+            }
+        }
+    } else if (ROWLANE) {
+        // ---------------- compute warp: lane = row, P sequences per lane ----------------
+        const bool active = lane < rows;
+        float R[P];
+        Rec<MT> rec_t[P];
+        Rec<MA> rec_a[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+            R[p] = active ? k.boot[(int64_t)(b0 + lane) * k.boot_sb + (int64_t)p * k.boot_sp] : 0.f;
+        int slot = 0;
+        uint32_t par = 0;
+        for (int i = 0; i < n; ++i) {
+            float* st = ring + slot * STAGE;
+            const int tl = min(RTC, k.T - (n - 1 - i) * RTC);
+            mbar_wait(full + slot, par);
+            if (active) {
+                float* pv = st + lane * RSV;
+                float* pr = st + TR * RSV + lane * RSV;
+                const float* prho = st + 2 * TR * RSV + lane * RSR;
+                scan_chunk_rowlane<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP>(pv, pr, prho, prho + TR * RSR, c_alias != 0, true,
+                                                                         tl, i == 0, rec_t, rec_a, R, k);
+            }
+            mbar_arrive(done + slot);
             if (++slot == ns) {
                 slot = 0;
                 par ^= 1;
@@ -664,14 +711,14 @@ int launch_dual(const ScanParams& k0, const ScanParams& k1, cudaStream_t st) {
 
 // Warp-specialised launch (k_target_rows_ws): one CTA of three warps per tile of 32/P rows, ring as deep as the
 // shared memory allows for the number of CTAs an SM has to hold.
-template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC>
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, int RTC, bool ROWLANE>
 int launch_ws(const ScanParams& k, cudaStream_t st) {
-    constexpr int TR = 32 / P;
+    constexpr int TR = ROWLANE ? 32 : 32 / P;
     constexpr int RSV = RTC * P + 4;
     constexpr int RSR = RTC * (RHO_PP ? P : 1) + 4;
     const bool alias = NEED_RHO && k.c.p == k.rho.p && k.c.sb == k.rho.sb && k.c.st == k.rho.st && k.c.sp == k.rho.sp;
     const size_t stage = sizeof(float) * TR * (2 * RSV + (NEED_RHO ? (alias ? RSR : 2 * RSR) : 0));
-    auto kern = k_target_rows_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, RTC>;
+    auto kern = k_target_rows_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, RTC, ROWLANE>;
     constexpr size_t BAR = WS_BAR_FLOATS * sizeof(float);
     static DevOnce once;
     const int sms = dev_setup(once, [&] {
@@ -702,12 +749,22 @@ inline int ws_row_bytes(int B) {
     return B >= wide ? 512 : 256;
 }
 
+// Which lane mapping the warp-specialised kernel uses by default (measured: profiles/r2_target_ws_rowlane.md).
+inline bool ws_rowlane_default(int B) { (void)B; return false; }
+
 // long rows: the warp-specialised kernel (16-row tiles at P = 2); rows of <= 64 steps: one warp per 32 x 16 tile
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
 int launch_rows(const ScanParams& k, cudaStream_t st) {
     if (k.T > B200RL_SHORT_T) {
-        if (ws_row_bytes(k.B) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P>(k, st);
-        return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P>(k, st);
+        // knob target_ws_rowlane = 0 / 1: lane = (row, player) with 32/P-row tiles / lane = row with 32-row tiles
+        long long rl = 0;
+        const bool rowlane = P > 1 && (b200rl_tuning(B200RL_TUNE_TARGET_WS_ROWLANE, &rl) ? rl != 0 : ws_rowlane_default(k.B));
+        if (rowlane) {
+            if (ws_row_bytes(k.B) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P, true>(k, st);
+            return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P, true>(k, st);
+        }
+        if (ws_row_bytes(k.B) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P, false>(k, st);
+        return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P, false>(k, st);
     }
     return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 32, 16>(k, st);
 }

@@ -29,6 +29,7 @@ int b200rl_version(void);
  * environment variable (B200RL_<NAME IN CAPITALS>), read once per process; `set` = 0 returns the knob to its built-in
  * default.  Knobs: rollout_chunk (plies per rollout ticket, 0 = static schedule), target_ws_stages (2..8),
  * target_ws_row (256 | 512 bytes per row and fetch), target_ws_wide_rows (batch rows from which 512 is used),
+ * target_ws_rowlane (0 = one (row, player) sequence per lane, 1 = one row per lane in the long-row kernel),
  * target_generic, target_no_dual, target_persistent (flags), emit_tma (0 = STG.128 emit path, 1 = staged bulk
  * stores; default: bulk stores for the Geister-sized tiles).  Results never depend on a knob.
  */
