@@ -93,7 +93,8 @@ def test_cs_is_rhos_same_tensor(B, T, P, rpp, vt, pt):
 
 @pytest.mark.parametrize("B,T,P,rpp", [(1000, 200, 2, False), (257, 128, 2, True), (333, 128, 1, False),
                                        (4096, 1024, 2, False), (17, 68, 2, False)])
-@pytest.mark.parametrize("vt,pt", [('TD', 'TD'), ('UPGO', 'UPGO'), ('VTRACE', 'VTRACE'), ('VTRACE', 'UPGO')])
+@pytest.mark.parametrize("vt,pt", [('TD', 'TD'), ('UPGO', 'UPGO'), ('VTRACE', 'VTRACE'), ('VTRACE', 'UPGO'),
+                                   ('UPGO', 'VTRACE'), ('TD', 'UPGO')])
 @pytest.mark.parametrize("head", ['value', 'return'])
 def test_long_rows_ws_kernel(monkeypatch, B, T, P, rpp, vt, pt, head):
     """Rows longer than 64 steps run in the warp-specialised kernel (loader / compute / storer warps, mbarrier
@@ -106,15 +107,18 @@ def test_long_rows_ws_kernel(monkeypatch, B, T, P, rpp, vt, pt, head):
     _, ra = targets_np.compute_target(pt, d['values'], d['returns'], d['rewards'], d['lmb'], d['gamma'], d['rhos'], d['cs'])
     g = _cuda(d)
     a = (g['values'], g['returns'], g['rewards'], g['lmb'], g['gamma'])
-    for rowlane in (0, 1):          # lane = (row, player) with 32/P-row tiles / lane = row with 32-row tiles
+    # three-warp kernel with lane = (row, player) / lane = row, and the four-warp staged pipeline
+    for rowlane, staged in ((0, 0), (1, 0), (0, 1)):
         for row in ('256', '512'):
             for stages in ('2', '5'):
+                _lib.set_tuning('target_ws_staged', staged)
                 _lib.set_tuning('target_ws_rowlane', rowlane)
                 _lib.set_tuning('target_ws_row', int(row))
                 _lib.set_tuning('target_ws_stages', int(stages))
                 try:
                     t1, a1 = compute_target_pair(vt, pt, *a, g['rhos'], g['cs'])
                 finally:
+                    _lib.set_tuning('target_ws_staged', None)
                     _lib.set_tuning('target_ws_rowlane', None)
                     _lib.set_tuning('target_ws_row', None)
                     _lib.set_tuning('target_ws_stages', None)
