@@ -37,7 +37,6 @@ Knob g_knobs[B200RL_TUNE_COUNT] = {
     {"target_persistent", "B200RL_TARGET_PERSISTENT", {0}, {0}},
     {"emit_tma", "B200RL_EMIT_TMA", {0}, {0}},
     {"target_ws_rowlane", "B200RL_TARGET_WS_ROWLANE", {0}, {0}},
-    {"target_ws_staged", "B200RL_TARGET_WS_STAGED", {0}, {0}},
 };
 }  // namespace
 

@@ -17,8 +17,7 @@ void b200rl_set_error(const char* fmt, ...);
 enum {
     B200RL_TUNE_ROLLOUT_CHUNK = 0, B200RL_TUNE_TARGET_WS_STAGES, B200RL_TUNE_TARGET_WS_ROW,
     B200RL_TUNE_TARGET_WS_WIDE_ROWS, B200RL_TUNE_TARGET_GENERIC, B200RL_TUNE_TARGET_NO_DUAL,
-    B200RL_TUNE_TARGET_PERSISTENT, B200RL_TUNE_EMIT_TMA, B200RL_TUNE_TARGET_WS_ROWLANE, B200RL_TUNE_TARGET_WS_STAGED,
-    B200RL_TUNE_COUNT
+    B200RL_TUNE_TARGET_PERSISTENT, B200RL_TUNE_EMIT_TMA, B200RL_TUNE_TARGET_WS_ROWLANE, B200RL_TUNE_COUNT
 };
 bool b200rl_tuning(int knob, long long* out);   // true when the knob is set (env or set_tuning)
 

@@ -620,8 +620,6 @@ __global__ void __launch_bounds__(96) k_target_rows_ws(const ScanParams k, int c
     }
 }
 
-#include "target_staged.cuh"
-
 }  // namespace
 
 namespace {
@@ -740,49 +738,6 @@ int launch_ws(const ScanParams& k, cudaStream_t st) {
     return b200rl_check_launch("k_target_rows_ws");
 }
 
-// Staged launch (k_target_rows_st, target_staged.cuh): one CTA of four warps per tile of 32/P rows.  `ns` as deep as
-// the shared memory allows while every tile stays resident; returns -1 when not even two slots fit.
-template <int MT, int MA, int P, bool HAS_REW, bool RHO_PP, int RTC>
-int launch_st(const ScanParams& k, bool alias, bool probe_only, cudaStream_t st) {
-    using L = StagedLayout<MT, MA, P, HAS_REW, RHO_PP, RTC>;
-    auto kern = k_target_rows_st<MT, MA, P, HAS_REW, RHO_PP, RTC>;
-    constexpr size_t BAR = ST_BAR_FLOATS * sizeof(float);
-    const size_t stage = sizeof(float) * (size_t)L::stage(alias);
-    static DevOnce once;
-    const int sms = dev_setup(once, [&] {
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WS_SMEM_CAP);
-    });
-    const int ntiles = (k.B + L::TR - 1) / L::TR;
-    const int want = (ntiles + sms - 1) / sms;   // CTAs an SM holds when the whole grid is resident
-    int ns = 0;
-    for (int c = 2; c <= WS_MAX_STAGES; ++c)
-        if ((size_t)want * (BAR + c * stage + 1024) <= (size_t)220 * 1024 && BAR + c * stage <= WS_SMEM_CAP) ns = c;
-    if (ns < 3 && probe_only) return -1;         // the caller tries a narrower chunk first
-    if (ns < 2) {
-        ns = 2;
-        if (BAR + ns * stage > WS_SMEM_CAP) return -1;
-    }
-    long long ns_knob = 0;
-    if (b200rl_tuning(B200RL_TUNE_TARGET_WS_STAGES, &ns_knob) && ns_knob >= 2 && ns_knob <= WS_MAX_STAGES &&
-        BAR + (size_t)ns_knob * stage <= WS_SMEM_CAP)
-        ns = (int)ns_knob;
-    kern<<<ntiles, 128, BAR + ns * stage, st>>>(k, alias ? 1 : 0, ns);
-    return b200rl_check_launch("k_target_rows_st");
-}
-
-// chunk of 128/P timesteps (512-byte raw rows) when three slots of it fit beside the other resident tiles, else 64/P
-template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
-int launch_staged(const ScanParams& k, cudaStream_t st) {
-    const bool alias = NEED_RHO && k.c.p == k.rho.p && k.c.sb == k.rho.sb && k.c.st == k.rho.st && k.c.sp == k.rho.sp;
-    long long v = 0;
-    const bool force_narrow = b200rl_tuning(B200RL_TUNE_TARGET_WS_ROW, &v) && v < 512;
-    if (!force_narrow) {
-        const int rc = launch_st<MT, MA, P, HAS_REW, RHO_PP, 128 / P>(k, alias, true, st);
-        if (rc >= 0) return rc;
-    }
-    return launch_st<MT, MA, P, HAS_REW, RHO_PP, 64 / P>(k, alias, false, st);
-}
-
 // Chunk width of the warp-specialised kernel: 256 B per row and fetch up to B200RL_TARGET_WS_WIDE_ROWS batch rows
 // (more chunks in flight per CTA while few CTAs share an SM), 512 B beyond (measured at B = 65,536: +3-9 % at
 // T = 200, +2-4 % at T = 1024; at B = 16,384 and T = 200 the wide chunks are 15 % slower).
@@ -794,26 +749,21 @@ inline int ws_row_bytes(int B) {
     return B >= wide ? 512 : 256;
 }
 
-// When the staged pipeline is the default (measured: profiles/r2_target_staged.md).
-inline bool ws_staged_default(int B, int P) { (void)B; (void)P; return false; }
-
 // Which lane mapping the warp-specialised kernel uses by default (measured: profiles/r2_target_ws_rowlane.md).
-inline bool ws_rowlane_default(int B) { (void)B; return false; }
+// Row per lane pays where the compute warp is the critical path AND its chain is short enough to be hidden behind the
+// second player's: TD / UPGO (no V-Trace in either role) on few tiles and long rows - 1024 x 4,096: value head
+// 0.68 -> 0.76 (TD), 0.61 -> 0.70 (UPGO) of the HBM peak, return head 0.78 -> 0.81 (TD).  At T = 200, with V-Trace
+// (11 fp32 instructions per sequence and step, each holding its pipe for 2 cycles) and at B >= 16,384 it is neutral
+// or slower.
+inline bool ws_rowlane_default(int B, int T, bool need_rho) { return !need_rho && T >= 512 && B <= 8192; }
 
 // long rows: the warp-specialised kernel (16-row tiles at P = 2); rows of <= 64 steps: one warp per 32 x 16 tile
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
 int launch_rows(const ScanParams& k, cudaStream_t st) {
     if (k.T > B200RL_SHORT_T) {
-        // knob target_ws_staged = 0 / 1: the four-warp staged pipeline (few tiles) / the three-warp kernel below
-        long long sg = 0;
-        const bool staged = b200rl_tuning(B200RL_TUNE_TARGET_WS_STAGED, &sg) ? sg != 0 : ws_staged_default(k.B, P);
-        if (staged) {
-            const int rc = launch_staged<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP>(k, st);
-            if (rc >= 0) return rc;
-        }
         // knob target_ws_rowlane = 0 / 1: lane = (row, player) with 32/P-row tiles / lane = row with 32-row tiles
         long long rl = 0;
-        const bool rowlane = P > 1 && (b200rl_tuning(B200RL_TUNE_TARGET_WS_ROWLANE, &rl) ? rl != 0 : ws_rowlane_default(k.B));
+        const bool rowlane = P > 1 && (b200rl_tuning(B200RL_TUNE_TARGET_WS_ROWLANE, &rl) ? rl != 0 : ws_rowlane_default(k.B, k.T, NEED_RHO));
         if (rowlane) {
             if (ws_row_bytes(k.B) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P, true>(k, st);
             return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P, true>(k, st);

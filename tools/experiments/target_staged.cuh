@@ -1,3 +1,7 @@
+// NOT PART OF THE BUILD.  An experiment kept for the record (profiles/r2_target_ws_rowlane.md section 3): bit-exact, but at
+// best break-even with k_target_rows_ws.  Commit b78b3bd has it wired into handyrl_b200/csrc/target_rows.cu (launcher
+// `launch_staged`, knob target_ws_staged, 60 long-row test cases).
+//
 // Staged pipeline for the target recursion when tiles are FEW (small B, long rows) - included by target_rows.cu
 // inside its anonymous namespace (it uses that file's cp.async / mbarrier / LaneIO helpers).
 //
