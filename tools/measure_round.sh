@@ -5,6 +5,7 @@ TAG=${1:-r1c}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
 timeout 600 python bench.py > $OUT/bench.json 2> $OUT/bench.err
 timeout 400 python bench.py --impl reference > $OUT/bench_ref.json 2> $OUT/bench_ref.err
 SWEEP_CPU=1 timeout 600 python tools/sweep_targets.py > $OUT/sweep.json 2> $OUT/sweep.txt
