@@ -685,8 +685,18 @@ extern "C" int b200rl_env_rollout(int game, void* state, int64_t N, int64_t n_pl
     B200RL_REQUIRE(!traj || D >= 1, "env_rollout: trajectory ring depth D must be >= 1");
     B200RL_REQUIRE(!ep_table || (E >= 1 && counters), "env_rollout: episode table needs E >= 1 and counters");
     B200RL_REQUIRE(((uintptr_t)ep_table % 16) == 0, "env_rollout: episode table must be 16-byte aligned");
-    B200RL_REQUIRE(N % 2 == 0 || waves <= 1 || !(out_main || out_scalar || out_amask),
-                   "env_rollout: N must be even when several waves are written (16-byte aligned wave bases)");
+    if (waves > 1 && (out_main || out_scalar || out_amask)) {
+        // wave w of a moment tensor starts at w * N * row floats and is written with 128-bit stores: every wave base
+        // must be 16-byte aligned (Geister: N even; TicTacToe, 27 + 9 floats per game: N a multiple of 4)
+        int64_t dims[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (b200rl_env_dims(game, dims) != B200RL_OK) return B200RL_ERR_ARG;
+        const int64_t A = dims[0], obits = dims[1], sbits = dims[2];
+        B200RL_REQUIRE((!out_main || (N * obits) % 4 == 0) && (!out_scalar || (N * sbits) % 4 == 0) &&
+                           (!out_amask || (N * A) % 4 == 0),
+                       "env_rollout: with several waves every wave base must be 16-byte aligned: N * floats-per-game "
+                       "(observation %lld, scalar %lld, action_mask %lld) must be a multiple of 4; N = %lld is not",
+                       (long long)obits, (long long)sbits, (long long)A, (long long)N);
+    }
     RolloutParams p;
     p.state = (uint32_t*)state; p.N = N; p.n_plies = n_plies; p.seed = seed; p.game_id_base = game_id_base;
     p.it0 = it0; p.out_main = out_main; p.out_scalar = out_scalar; p.out_amask = out_amask;

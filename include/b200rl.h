@@ -180,7 +180,8 @@ int b200rl_env_step_observe(int game, void* state, int64_t N, const int32_t* act
  * game with auto-reset; every game performs exactly one env-step per ply.
  *   seed, game_id_base, it0 : counter-RNG key (seed, game_id_base + slot, it0 + ply)
  *   out_main/out_scalar/out_amask/out_action : moment data of ply `it`, written to wave
- *       (it % waves) of [waves][N][...] buffers; any may be NULL
+ *       (it % waves) of [waves][N][...] buffers; any may be NULL.  With waves > 1 every wave base must be 16-byte
+ *       aligned: N * floats-per-game a multiple of 4 (Geister: N even; TicTacToe: N a multiple of 4), else ERR_ARG
  *   traj : [N][D] slot-major ring of 32-byte compact records (8 x uint32, 32-byte aligned): record of
  *          (iteration it, slot i) at (i * D + it % D) * 32 bytes, or NULL
  *   ep_table : (E, 4) int32 ring of finished episodes {slot, steps | win << 16, end_it lo, hi}

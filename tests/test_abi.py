@@ -40,6 +40,21 @@ def test_argument_errors_do_not_need_a_gpu():
     assert st != 0 and b"null" in h.b200rl_last_error()
 
 
+def test_rollout_rejects_misaligned_wave_bases_before_launching():
+    """Several waves are written with 128-bit stores: N = 130 TicTacToe games would put wave 1 of the observation at
+    130 * 27 * 4 bytes (not a multiple of 16) - found by tools/sanitize_smoke.py as a 'misaligned address' fault in the
+    kernel when the check only asked for an even N.  The pointers are never dereferenced: validation comes first."""
+    h = _lib.lib()
+    fake = ctypes.c_void_p(0x10000)
+    for game, n, ok in ((0, 130, False), (0, 132, True), (2, 130, True), (2, 131, False)):
+        rc = h.b200rl_env_rollout(game, fake, n, 0 if ok else 8, 1, 0, 0, fake, None if game == 0 else fake, fake, None, 2,
+                                  None, 0, None, 0, None, fake, 1 << 20, None)
+        if ok:
+            assert rc == 0, h.b200rl_last_error()       # n_plies = 0: validated, nothing launched
+        else:
+            assert rc != 0 and b"multiple of 4" in h.b200rl_last_error()
+
+
 def test_no_cpu_fallback():
     import pytest
     import torch
