@@ -152,6 +152,68 @@ __device__ __forceinline__ void emit_flat_f32(const uint32_t* __restrict__ flat,
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// Rows shorter than one word, one row per lane (TicTacToe: 27 observation bits and 9 mask bits per game).  The 32
+// rows of a warp are only NB words of flat string, so the whole tile fits in ONE register per lane: lane w builds
+// flat word w from the <= SPAN rows that overlap bits [32w, 32w + 32) with shuffles, and float4 q = lane + 32u of the
+// tile is nibble (lane & 7) of word (lane >> 3) + 4u, fetched by one more shuffle.  No shared memory, no atomicOr, no
+// __syncwarp, and the store predicate of a full tile is a compile-time constant.  The TicTacToe rollout is bound by
+// instruction latency at low occupancy (2,048 warps for 65,536 games), not by HBM: the flat-string-in-shared path above
+// cost it ~300 of its 656 warp instructions per ply (profiles/r2_ttt_rollout.md).  Same bytes as emit_flat_f32.
+// All 32 lanes must call; lanes >= rows pass zero bits.
+// ---------------------------------------------------------------------------------------------------------------
+template <int NB>
+__device__ __forceinline__ uint32_t short_rows_word(uint32_t bits, int lane) {
+    static_assert(NB >= 1 && NB < 32, "rows shorter than one word");
+    constexpr int SPAN = (NB + 30) / NB + 1;   // rows a 32-bit window starting inside a row can touch
+    const int p = 32 * lane, r0 = p / NB, o = p - r0 * NB;
+    uint32_t w = 0;
+#pragma unroll
+    for (int j = 0; j < SPAN; ++j) {
+        const int r = r0 + j;
+        uint32_t b = __shfl_sync(0xffffffffu, bits, r & 31);
+        const int sh = j * NB - o;             // where bit 0 of row r lands in this word (negative only for j = 0)
+        // sh <= j * NB, so only the last rows of the span can start past the word; rows >= 32 (which wrap around in
+        // the shuffle) only ever reach the words of lanes >= NB, which nobody reads
+        if (j * NB >= 32 && sh >= 32) b = 0u;
+        w |= j == 0 ? b >> o : b << (sh & 31);
+    }
+    return w;
+}
+
+// `tbl` = the 16 nibble images of (v0, v1) in shared memory (nibble_table_init): one LDS.128 per float4 instead of
+// the ~8 ALU instructions of nibble_expand - this path is bound by instruction issue, its LSU pipe is at 13 %.
+template <int NB>
+__device__ __forceinline__ void emit_short_rows_f32(uint32_t bits, const float4* __restrict__ tbl,
+                                                    float* __restrict__ out_tile, int rows, int lane, float v0,
+                                                    float v1) {
+    const uint32_t word = short_rows_word<NB>(bits, lane);
+    constexpr int N4 = 8 * NB;                 // float4 of a full tile of 32 rows
+    constexpr int IT = (N4 + 31) / 32;
+    static_assert(3 + 4 * (IT - 1) < 32, "source lanes of the word shuffles");
+    const int sh = (lane & 7) << 2, src = lane >> 3;
+    float4* o4 = reinterpret_cast<float4*>(out_tile);
+    if (rows == 32) {
+#pragma unroll
+        for (int u = 0; u < IT; ++u) {
+            const float4 f = tbl[(__shfl_sync(0xffffffffu, word, src + 4 * u) >> sh) & 15u];
+            if (32 * u + 32 <= N4) st_stream_f4(o4 + lane + 32 * u, f);
+            else if (lane < N4 - 32 * u) st_stream_f4(o4 + lane + 32 * u, f);
+        }
+        return;
+    }
+    // the ragged last group of a batch
+    const int total = rows * NB, n4 = total >> 2;
+#pragma unroll
+    for (int u = 0; u < IT; ++u) {
+        const float4 f = tbl[(__shfl_sync(0xffffffffu, word, src + 4 * u) >> sh) & 15u];
+        if (lane + 32 * u < n4) st_stream_f4(o4 + lane + 32 * u, f);
+    }
+    const int e = (n4 << 2) + lane;            // < 4 floats left
+    const uint32_t wv = __shfl_sync(0xffffffffu, word, (e >> 5) & 31);
+    if (e < total) out_tile[e] = ((wv >> (e & 31)) & 1u) ? v1 : v0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // TMA variant of the streaming loop (profiles/r2_probe_write_tma.txt: 7.04 -> 7.3-7.45 TB/s on the same tiles).
 // The warp expands the tile chunk by chunk into a private ring of NBUF staging buffers in shared memory
 // (st.shared.v4, lane q -> float4 q: conflict-free) and ONE lane hands each finished chunk to the copy engine:

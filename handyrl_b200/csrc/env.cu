@@ -121,6 +121,19 @@ __device__ __forceinline__ void emit_views(CtaStage<G>& cta, int warp, const typ
     for (int k = 0; k < G::OW; ++k) ob[k] = 0;
 #pragma unroll
     for (int k = 0; k < G::LW; ++k) lm[k] = 0;
+    if constexpr (G::OBITS < 32 && G::A < 32 && G::SBITS == 0) {
+        // TicTacToe: the whole tile is one register per lane, packed and streamed with shuffles (emit.cuh)
+        if (!tma) {
+            if (valid) {
+                if (want_obs) G::obs_bits(s, view, ob, sc[0]);
+                if (want_legal) G::legal_bits(s, lm);
+                if (out_bits) out_bits[g0 + lane] = lm[0];
+            }
+            if (out_main) emit_short_rows_f32<G::OBITS>(ob[0], cta.tbl_obs, out_main + g0 * G::OBITS, ng, lane, 0.f, 1.f);
+            if (out_amask) emit_short_rows_f32<G::A>(lm[0], cta.tbl_amask, out_amask + g0 * G::A, ng, lane, 1e32f, 0.f);
+            return;
+        }
+    }
     if (valid) {
         if (want_obs) G::obs_bits(s, view, ob, sc[0]);
         if (want_legal) G::legal_bits(s, lm);
@@ -393,6 +406,18 @@ __global__ void __launch_bounds__(BLK, TMA ? 5 : 8) k_rollout(const RolloutParam
         const uint64_t stream_id = p.game_id_base + (uint64_t)i;
         const int64_t k_begin = ch * p.chunk, k_end = min(k_begin + p.chunk, p.n_plies);
 
+        // Wave of the current ply and the element offsets of its output tiles.  The general form derives them from
+        // the iteration number every ply (a remainder and three 64-bit products: noise for Geister, whose warp writes
+        // 60 KB per ply); games with rows shorter than a word (TicTacToe: 5.6 KB per warp and ply, bound by
+        // instruction issue at 2,048 warps - profiles/r2_ttt_rollout.md) advance them by one wave per ply instead.
+        constexpr bool LIGHT = G::OBITS < 32 && G::SBITS == 0;
+        int64_t wv = 0, wv_main = 0, wv_amask = 0, wv_act = 0;
+        if constexpr (LIGHT) {
+            wv = p.waves > 0 ? (int64_t)ring_mod(p.it0 + (uint64_t)k_begin, (uint64_t)p.waves) : 0;
+            wv_main = wv * p.N * G::OBITS;
+            wv_amask = wv * p.N * G::A;
+            wv_act = wv * p.N;
+        }
         for (int64_t k = k_begin; k < k_end; ++k) {
             const uint64_t it = p.it0 + (uint64_t)k;
             bool first = false;
@@ -413,18 +438,18 @@ __global__ void __launch_bounds__(BLK, TMA ? 5 : 8) k_rollout(const RolloutParam
                 action = kth_set_bit<G::LW, G::A>(lm, kk);
                 selp = (int)((r >> 7) & 1);  // ParallelTicTacToe: which player's move lands
             }
-            const int64_t wv = p.waves > 0 ? (int64_t)ring_mod(it, (uint64_t)p.waves) : 0;
+            if constexpr (!LIGHT) wv = p.waves > 0 ? (int64_t)ring_mod(it, (uint64_t)p.waves) : 0;
             if (p.out_main || p.out_amask || p.out_scalar) {
                 emit_views<G>(stage, warp, s, valid, B200RL_VIEW_TURN, g0, ng, lane,
-                              p.out_main ? p.out_main + wv * p.N * G::OBITS : nullptr,
+                              p.out_main ? p.out_main + (LIGHT ? wv_main : wv * p.N * G::OBITS) : nullptr,
                               p.out_scalar ? p.out_scalar + wv * p.N * G::SBITS : nullptr,
-                              p.out_amask ? p.out_amask + wv * p.N * G::A : nullptr, nullptr,
+                              p.out_amask ? p.out_amask + (LIGHT ? wv_amask : wv * p.N * G::A) : nullptr, nullptr,
                               TMA ? &tma_stage : nullptr);
             }
             bool term = false;
             uint32_t wincode = 0;
             if (valid) {
-                if (p.out_action) p.out_action[wv * p.N + i] = action;
+                if (p.out_action) p.out_action[(LIGHT ? wv_act : wv * p.N) + i] = action;
                 uint32_t rec[8];
                 if (p.traj) G::pack_record(s, rec);
                 G::step(s, action, selp);
@@ -491,6 +516,15 @@ __global__ void __launch_bounds__(BLK, TMA ? 5 : 8) k_rollout(const RolloutParam
                     }
                     rec_fill = 0;
                     __syncwarp();
+                }
+            }
+            if constexpr (LIGHT) {
+                if (++wv >= p.waves) {
+                    wv = wv_main = wv_amask = wv_act = 0;
+                } else {
+                    wv_main += p.N * G::OBITS;
+                    wv_amask += p.N * G::A;
+                    wv_act += p.N;
                 }
             }
         }
