@@ -387,6 +387,29 @@ __global__ void __launch_bounds__(BLK) k_make_batch(const BatchParams p) {
     // rows of >= 32 bits (Geister): shuffle-merged packing, every lane takes part (invalid lanes carry zero bits);
     // shorter rows (TicTacToe, the 18 scalar bits): atomicOr packing after a clearing pass
     constexpr bool BIG_O = G::OBITS >= 32, BIG_A = G::A >= 32;
+    if constexpr (G::OBITS < 32 && G::A < 16 && G::SBITS == 0 && !TMA) {
+        // TicTacToe.  The Po rows of a lane are neighbours in the flat string, so a lane owns ONE row of Po x NB bits:
+        // mask and policy tiles (9 or 18 bits per lane) and the one-player observation tile (27) stay in one register
+        // per lane and are packed and streamed with shuffles (emit_short_rows_f32); two players' 54 observation bits
+        // take the shuffle-merged path of rows >= 32 bits.  No clearing pass, no atomicOr.
+        if (Po == 1) {
+            emit_short_rows_f32<G::OBITS>(ob[0][0], cta.tbl_obs, p.obs_main + c0 * G::OBITS, nc, lane, 0.f, 1.f);
+            emit_short_rows_f32<G::A>(lg[0][0], cta.tbl_amask, p.amask + c0 * G::A, nc, lane, 1e32f, 0.f);
+            if (rnd_policy)
+                emit_short_rows_f32<G::A>(il[0][0], cta.tbl_policy, p.policy + c0 * G::A, nc, lane, 0.f, -1e32f);
+        } else {
+            const uint32_t o2[2] = {ob[0][0] | (ob[1][0] << G::OBITS), ob[1][0] >> (32 - G::OBITS)};
+            flat_pack_warp<2 * G::OBITS, 2>(st.obs, lane, nc, o2);
+            __syncwarp();
+            emit_flat_f32<2 * G::OBITS>(st.obs, cta.tbl_obs, p.obs_main + c0 * 2 * G::OBITS, nc, lane, 0.f, 1.f);
+            emit_short_rows_f32<2 * G::A>(lg[0][0] | (lg[1][0] << G::A), cta.tbl_amask, p.amask + c0 * 2 * G::A, nc,
+                                          lane, 1e32f, 0.f);
+            if (rnd_policy)
+                emit_short_rows_f32<2 * G::A>(il[0][0] | (il[1][0] << G::A), cta.tbl_policy, p.policy + c0 * 2 * G::A,
+                                              nc, lane, 0.f, -1e32f);
+        }
+        return;
+    }
     if (valid) {
         for (int q = 0; q < Po; ++q) {
             const int row = lane * Po + q;
