@@ -145,14 +145,15 @@ __device__ __forceinline__ void flush_full(const float* tile, float* __restrict_
 }
 
 // Four timesteps (descending) of the P sequences of one row.  FIRST: the group contains t = T-1 at j = 3.
-template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, bool FIRST>
+// JHI..JLO: the timesteps of the group to process (the row-per-lane pipeline below works in halves).
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP, bool FIRST, int JHI = 3, int JLO = 0>
 __device__ __forceinline__ void scan_group(const float (&v)[4 * P], const float (&rw)[4 * P],
                                            const float (&rho)[4 * (RHO_PP ? P : 1)],
                                            const float (&cc)[4 * (RHO_PP ? P : 1)], Rec<MT> (&rec_t)[P],
                                            Rec<MA> (&rec_a)[P], const float (&R)[P], const ScanParams& k,
                                            float (&tg)[4 * P], float (&ad)[4 * P]) {
 #pragma unroll
-    for (int j = 3; j >= 0; --j) {
+    for (int j = JHI; j >= JLO; --j) {
 #pragma unroll
         for (int p = 0; p < P; ++p) {
             const int i = j * P + p;
@@ -254,6 +255,103 @@ __device__ __forceinline__ void scan_chunk_rowlane(float* pv, float* pr, const f
         compute_group(gb, q - 1, std::false_type{});
     }
     if (q == 0) compute_group(ga, 0, std::false_type{});
+}
+
+#ifndef B200RL_ROWLANE_V2
+#define B200RL_ROWLANE_V2 1
+#endif
+// scan_chunk_rowlane for the warp-specialised kernel at P = 2, with the order of the shared-memory instructions pinned
+// (volatile accesses keep their program order through ptxas).  Why (profiles/r2_target_ws_rowlane.md, section 5): in the
+// version above ptxas issues the LDS.128 batch of the next group next to the first uses of the current one and gives both
+// the same scoreboard, so a consumer of completed loads also waits ~29 cycles for the fresh ones; and it overwrites the
+// source registers of an STS.128 a few instructions after the store, which then waits for the store to read them.  Here a
+// group of four timesteps is computed in two halves and the memory instructions sit between them:
+//     steps 3,2 of group q | STS results of group q+1 | LDS inputs of group q-1 | steps 1,0 of group q
+// with two input and two result register sets, so loads are consumed half a group after they were issued (and only one
+// batch is ever outstanding) and result registers are rewritten half a group after their store.
+template <int MT, int MA, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
+__device__ __forceinline__ void scan_chunk_rowlane_v2(float* pv, float* pr, const float* prho, const float* pc,
+                                                      bool c_alias, int tl, bool first_chunk, Rec<MT> (&rec_t)[2],
+                                                      Rec<MA> (&rec_a)[2], const float (&R)[2], const ScanParams& k) {
+    constexpr int P = 2;
+    constexpr int WR = RHO_PP ? P : 1;
+    struct In { float v[4 * P], r[4 * P], rho[4 * WR], c[4 * WR]; };
+    struct Out { float t[4 * P], a[4 * P]; };
+    auto lds4 = [](const float* p, float* d) {
+        asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+                     : "r"((uint32_t)__cvta_generic_to_shared(p)));
+    };
+    auto sts4 = [](float* p, const float* d) {
+        asm volatile("st.volatile.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"((uint32_t)__cvta_generic_to_shared(p)),
+                     "f"(d[0]), "f"(d[1]), "f"(d[2]), "f"(d[3]));
+    };
+    auto load = [&](In& g, int q) {
+#pragma unroll
+        for (int u = 0; u < P; ++u) {
+            lds4(pv + q * 4 * P + 4 * u, g.v + 4 * u);
+            if (HAS_REW) lds4(pr + q * 4 * P + 4 * u, g.r + 4 * u);
+        }
+        if (NEED_RHO) {
+#pragma unroll
+            for (int u = 0; u < WR; ++u) {
+                lds4(prho + q * 4 * WR + 4 * u, g.rho + 4 * u);
+                if (!c_alias) lds4(pc + q * 4 * WR + 4 * u, g.c + 4 * u);
+            }
+        }
+    };
+    auto store = [&](const Out& o, int q) {
+#pragma unroll
+        for (int u = 0; u < P; ++u) {
+            sts4(pv + q * 4 * P + 4 * u, o.a + 4 * u);
+            sts4(pr + q * 4 * P + 4 * u, o.t + 4 * u);
+        }
+    };
+    // one group: cur -> res; `prev` = results of group q + 1 still in registers, `nxt` = inputs of group q - 1
+    auto body = [&](In& cur, Out& res, In& nxt, const Out& prev, int q, auto first_tag, auto store_prev, auto load_next) {
+        constexpr bool FIRST = decltype(first_tag)::value;
+        if (NEED_RHO && c_alias) {
+#pragma unroll
+            for (int i = 0; i < 4 * WR; ++i) cur.c[i] = cur.rho[i];
+        }
+        scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, FIRST, 3, 2>(cur.v, cur.r, cur.rho, cur.c, rec_t, rec_a, R, k,
+                                                                        res.t, res.a);
+        if (decltype(store_prev)::value) store(prev, q + 1);
+        if (decltype(load_next)::value) load(nxt, q - 1);
+        scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, false, 1, 0>(cur.v, cur.r, cur.rho, cur.c, rec_t, rec_a, R, k,
+                                                                        res.t, res.a);
+    };
+    using Y = std::true_type;
+    using N = std::false_type;
+    In ia, ib;
+    Out ra, rb;
+    if (!HAS_REW) {
+#pragma unroll
+        for (int i = 0; i < 4 * P; ++i) ia.r[i] = ib.r[i] = 0.f;
+    }
+    const int Q = tl >> 2;
+    load(ia, Q - 1);
+    if (Q == 1) {
+        if (first_chunk) body(ia, ra, ib, rb, 0, Y{}, N{}, N{});
+        else body(ia, ra, ib, rb, 0, N{}, N{}, N{});
+        store(ra, 0);
+        return;
+    }
+    if (first_chunk) body(ia, ra, ib, rb, Q - 1, Y{}, N{}, Y{});
+    else body(ia, ra, ib, rb, Q - 1, N{}, N{}, Y{});
+    int q = Q - 2;
+    for (; q >= 2; q -= 2) {
+        body(ib, rb, ia, ra, q, N{}, Y{}, Y{});
+        body(ia, ra, ib, rb, q - 1, N{}, Y{}, Y{});
+    }
+    if (q == 1) {
+        body(ib, rb, ia, ra, 1, N{}, Y{}, Y{});
+        body(ia, ra, ib, rb, 0, N{}, Y{}, N{});
+        store(ra, 0);
+    } else {
+        body(ib, rb, ia, ra, 0, N{}, Y{}, N{});
+        store(rb, 0);
+    }
 }
 
 // ns = ring depth (2..4 stages): 2 when the grid fills the SMs (more resident warps hide the latency better than
@@ -517,8 +615,18 @@ __global__ void __launch_bounds__(96) k_target_rows_ws(const ScanParams k, int c
                 float* pv = st + lane * RSV;
                 float* pr = st + TR * RSV + lane * RSV;
                 const float* prho = st + 2 * TR * RSV + lane * RSR;
-                scan_chunk_rowlane<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP>(pv, pr, prho, prho + TR * RSR, c_alias != 0, true,
-                                                                         tl, i == 0, rec_t, rec_a, R, k);
+                // pinned-order version where it measured faster (1024 x 4,096, same box): with V-Trace in either role
+                // (0.63 -> 0.66 value head, 0.67 -> 0.75 return head, fused pair 0.53 -> 0.58 / 0.64 -> 0.68) and TD with
+                // rewards (0.81 -> 0.89); TD / UPGO without rewards and UPGO with rewards keep the plain version
+                // (0.76 / 0.69 / 0.72 against 0.73 / 0.63 / 0.70)
+                constexpr bool V2 = B200RL_ROWLANE_V2 != 0 && P == 2 &&
+                                    (NEED_RHO || (HAS_REW && MT == B200RL_TARGET_TD && MA == B200RL_TARGET_TD));
+                if constexpr (V2)
+                    scan_chunk_rowlane_v2<MT, MA, HAS_REW, NEED_RHO, RHO_PP>(pv, pr, prho, prho + TR * RSR, c_alias != 0,
+                                                                             tl, i == 0, rec_t, rec_a, R, k);
+                else
+                    scan_chunk_rowlane<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP>(pv, pr, prho, prho + TR * RSR, c_alias != 0, true,
+                                                                             tl, i == 0, rec_t, rec_a, R, k);
             }
             mbar_arrive(done + slot);
             if (++slot == ns) {
@@ -750,12 +858,15 @@ inline int ws_row_bytes(int B) {
 }
 
 // Which lane mapping the warp-specialised kernel uses by default (measured: profiles/r2_target_ws_rowlane.md).
-// Row per lane pays where the compute warp is the critical path AND its chain is short enough to be hidden behind the
-// second player's: TD / UPGO (no V-Trace in either role) on few tiles and long rows - 1024 x 4,096: value head
-// 0.68 -> 0.76 (TD), 0.61 -> 0.70 (UPGO) of the HBM peak, return head 0.78 -> 0.81 (TD).  At T = 200, with V-Trace
-// (11 fp32 instructions per sequence and step, each holding its pipe for 2 cycles) and at B >= 16,384 it is neutral
-// or slower.
-inline bool ws_rowlane_default(int B, int T, bool need_rho) { return !need_rho && T >= 512 && B <= 8192; }
+// Row per lane pays where the compute warp is the critical path: few tiles and long rows.  1024 x 4,096, fraction of the
+// HBM peak, sequence per lane -> row per lane: TD 0.68 -> 0.76 (value head) / 0.79 -> 0.89 (return head), UPGO
+// 0.61 -> 0.69 / 0.73 -> 0.72, V-Trace 0.62 -> 0.66 / 0.67 -> 0.75, V-Trace + UPGO 0.53 -> 0.58 / 0.61 -> 0.68 (the
+// V-Trace and TD-with-rewards numbers need the pinned-order scan, scan_chunk_rowlane_v2); T = 512 / 2048 and B = 8,192
+// gain the same 5-20 %.  At T = 200, at B >= 16,384 and at B = 2,048 (64 tiles) it is neutral or slower.
+inline bool ws_rowlane_default(int B, int T, bool need_rho) {
+    (void)need_rho;
+    return T >= 512 && B > 2048 && B <= 8192;
+}
 
 // long rows: the warp-specialised kernel (16-row tiles at P = 2); rows of <= 64 steps: one warp per 32 x 16 tile
 template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
