@@ -9,8 +9,8 @@ typedef unsigned long long u64;
 #define ITERS 4096
 
 template <int OP, int CH>
-__global__ void k(const float* in, float* out, long long* cyc) {
-    float a[CH], b = in[33];
+__global__ void k(const float* in, float* out, long long* cyc, float bparam) {
+    float a[CH], b = OP >= 6 ? bparam : in[33];   // OP 6 / 7: the multiplier comes from a kernel parameter (uniform register)
     u64 p[CH], q;
     for (int i = 0; i < CH; ++i) {
         a[i] = in[threadIdx.x + i];
@@ -30,6 +30,8 @@ __global__ void k(const float* in, float* out, long long* cyc) {
                 if (OP == 3) asm volatile("add.rn.f32x2 %0, %0, %1;" : "+l"(p[i]) : "l"(q));
                 if (OP == 4) asm volatile("fma.rn.f32x2 %0, %0, %1, %1;" : "+l"(p[i]) : "l"(q));
                 if (OP == 5) a[i] = fmaxf(a[i], b);
+                if (OP == 6) a[i] = __fmul_rn(a[i], b);
+                if (OP == 7) a[i] = __fadd_rn(a[i], b);
             }
         }
     }
@@ -46,8 +48,8 @@ __global__ void k(const float* in, float* out, long long* cyc) {
 
 template <int OP, int CH>
 void run(const char* name, float* in, float* out, long long* cyc) {
-    k<OP, CH><<<1, 32>>>(in, out, cyc);
-    k<OP, CH><<<1, 32>>>(in, out, cyc);
+    k<OP, CH><<<1, 32>>>(in, out, cyc, 1.0001f);
+    k<OP, CH><<<1, 32>>>(in, out, cyc, 1.0001f);
     cudaDeviceSynchronize();
     long long c;
     cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
@@ -67,5 +69,8 @@ int main() {
     run<3, 1>("FADD2", in, out, cyc); run<3, 8>("FADD2", in, out, cyc);
     run<4, 1>("FFMA2", in, out, cyc); run<4, 8>("FFMA2", in, out, cyc);
     run<5, 1>("FMNMX", in, out, cyc); run<5, 8>("FMNMX", in, out, cyc);
+    run<6, 1>("FMUL.UR", in, out, cyc); run<6, 8>("FMUL.UR", in, out, cyc); run<6, 2>("FMUL.UR", in, out, cyc); run<6, 4>("FMUL.UR", in, out, cyc);
+    run<7, 1>("FADD.UR", in, out, cyc); run<7, 8>("FADD.UR", in, out, cyc);
+    run<0, 2>("FMUL", in, out, cyc); run<0, 4>("FMUL", in, out, cyc);
     return 0;
 }
