@@ -257,6 +257,131 @@ __device__ __forceinline__ void scan_chunk_rowlane(float* pv, float* pr, const f
     if (q == 0) compute_group(ga, 0, std::false_type{});
 }
 
+// Driver of the pinned-order scans below.  Q >= 1 groups of four timesteps, processed from group Q-1 down to 0 with two
+// input (ia, ib) and two result (ra, rb) register sets in ping-pong:
+//     body(cur, res, nxt, prev, q, first, store_prev, load_next) =
+//         steps 3,2 of group q | store(prev, q+1) | load(nxt, q-1) | steps 1,0 of group q
+// The loop is unrolled by two so every set is addressed statically; first / store_prev / load_next are tag types.
+template <class In, class Out, class Load, class Store, class Body>
+__device__ __forceinline__ void pinned_order_groups(int Q, bool first_chunk, In& ia, In& ib, Out& ra, Out& rb, Load load,
+                                                    Store store, Body body) {
+    using Y = std::true_type;
+    using N = std::false_type;
+    load(ia, Q - 1);
+    if (Q == 1) {
+        if (first_chunk) body(ia, ra, ib, rb, 0, Y{}, N{}, N{});
+        else body(ia, ra, ib, rb, 0, N{}, N{}, N{});
+        store(ra, 0);
+        return;
+    }
+    if (first_chunk) body(ia, ra, ib, rb, Q - 1, Y{}, N{}, Y{});
+    else body(ia, ra, ib, rb, Q - 1, N{}, N{}, Y{});
+    int q = Q - 2;
+    for (; q >= 2; q -= 2) {
+        body(ib, rb, ia, ra, q, N{}, Y{}, Y{});
+        body(ia, ra, ib, rb, q - 1, N{}, Y{}, Y{});
+    }
+    if (q == 1) {
+        body(ib, rb, ia, ra, 1, N{}, Y{}, Y{});
+        body(ia, ra, ib, rb, 0, N{}, Y{}, N{});
+        store(ra, 0);
+    } else {
+        body(ib, rb, ia, ra, 0, N{}, Y{}, N{});
+        store(rb, 0);
+    }
+}
+
+__device__ __forceinline__ float lds_volatile(const float* p) {
+    float r;
+    asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(r) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+    return r;
+}
+__device__ __forceinline__ void sts_volatile(float* p, float v) {
+    asm volatile("st.volatile.shared.f32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "f"(v));
+}
+__device__ __forceinline__ void lds4_volatile(const float* p, float* d) {
+    asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+                 : "r"((uint32_t)__cvta_generic_to_shared(p)));
+}
+__device__ __forceinline__ void sts4_volatile(float* p, const float* d) {
+    asm volatile("st.volatile.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "f"(d[0]),
+                 "f"(d[1]), "f"(d[2]), "f"(d[3]));
+}
+
+// One chunk of `tl` timesteps (a multiple of 4) of ONE (row, player) sequence held by this lane, in pinned order (see
+// scan_chunk_rowlane_v2 below for why).  pv / pr point at this sequence's first element in the row-major [t][p] slivers
+// (stride P floats per timestep); prho / pc at its rho / c (stride WR).
+template <int MT, int MA, int P, bool HAS_REW, bool NEED_RHO, bool RHO_PP>
+__device__ __forceinline__ void scan_chunk_seqlane_v2(float* pv, float* pr, const float* prho, const float* pc,
+                                                      bool c_alias, int tl, bool first_chunk, Rec<MT>& rec_t,
+                                                      Rec<MA>& rec_a, float R, const ScanParams& k) {
+    constexpr int WR = RHO_PP ? P : 1;
+    struct In { float v[4], r[4], rho[4], c[4]; };
+    struct Out { float t[4], a[4]; };
+    auto load = [&](In& g, int q) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            g.v[j] = lds_volatile(pv + (q * 4 + j) * P);
+            if (HAS_REW) g.r[j] = lds_volatile(pr + (q * 4 + j) * P);
+        }
+        if (NEED_RHO) {
+            if (WR == 1) {   // rho / c broadcast over players: 4 steps are one 16-byte unit
+                lds4_volatile(prho + q * 4, g.rho);
+                if (!c_alias) lds4_volatile(pc + q * 4, g.c);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    g.rho[j] = lds_volatile(prho + (q * 4 + j) * WR);
+                    if (!c_alias) g.c[j] = lds_volatile(pc + (q * 4 + j) * WR);
+                }
+            }
+        }
+    };
+    auto store = [&](const Out& o, int q) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            sts_volatile(pv + (q * 4 + j) * P, o.a[j]);
+            sts_volatile(pr + (q * 4 + j) * P, o.t[j]);
+        }
+    };
+    auto steps = [&](const In& g, Out& o, auto first_tag, auto hi_tag) {
+        constexpr bool FIRST = decltype(first_tag)::value;
+        constexpr int JHI = decltype(hi_tag)::value ? 3 : 1;
+#pragma unroll
+        for (int j = JHI; j >= JHI - 1; --j) {
+            const float r_ = HAS_REW ? g.r[j] : 0.f;
+            const float rh = NEED_RHO ? g.rho[j] : 0.f;
+            const float c_ = NEED_RHO ? (c_alias ? g.rho[j] : g.c[j]) : 0.f;
+            float t1, a1, t2, a2;
+            if (FIRST && j == 3) {
+                rec_t.first(g.v[j], r_, rh, c_, R, k, t1, a1);
+                if (MT != MA) {
+                    rec_a.first(g.v[j], r_, rh, c_, R, k, t2, a2);
+                    a1 = a2;
+                }
+            } else {
+                rec_t.next(g.v[j], r_, rh, c_, k, t1, a1);
+                if (MT != MA) {
+                    rec_a.next(g.v[j], r_, rh, c_, k, t2, a2);
+                    a1 = a2;
+                }
+            }
+            o.t[j] = t1;
+            o.a[j] = a1;
+        }
+    };
+    auto body = [&](In& cur, Out& res, In& nxt, const Out& prev, int q, auto first_tag, auto store_prev, auto load_next) {
+        steps(cur, res, first_tag, std::true_type{});
+        if (decltype(store_prev)::value) store(prev, q + 1);
+        if (decltype(load_next)::value) load(nxt, q - 1);
+        steps(cur, res, std::false_type{}, std::false_type{});
+    };
+    In ia, ib;
+    Out ra, rb;
+    pinned_order_groups(tl >> 2, first_chunk, ia, ib, ra, rb, load, store, body);
+}
+
 #ifndef B200RL_ROWLANE_V2
 #define B200RL_ROWLANE_V2 1
 #endif
@@ -277,15 +402,8 @@ __device__ __forceinline__ void scan_chunk_rowlane_v2(float* pv, float* pr, cons
     constexpr int WR = RHO_PP ? P : 1;
     struct In { float v[4 * P], r[4 * P], rho[4 * WR], c[4 * WR]; };
     struct Out { float t[4 * P], a[4 * P]; };
-    auto lds4 = [](const float* p, float* d) {
-        asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
-                     : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
-                     : "r"((uint32_t)__cvta_generic_to_shared(p)));
-    };
-    auto sts4 = [](float* p, const float* d) {
-        asm volatile("st.volatile.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"((uint32_t)__cvta_generic_to_shared(p)),
-                     "f"(d[0]), "f"(d[1]), "f"(d[2]), "f"(d[3]));
-    };
+    auto lds4 = [](const float* p, float* d) { lds4_volatile(p, d); };
+    auto sts4 = [](float* p, const float* d) { sts4_volatile(p, d); };
     auto load = [&](In& g, int q) {
 #pragma unroll
         for (int u = 0; u < P; ++u) {
@@ -321,37 +439,13 @@ __device__ __forceinline__ void scan_chunk_rowlane_v2(float* pv, float* pr, cons
         scan_group<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, false, 1, 0>(cur.v, cur.r, cur.rho, cur.c, rec_t, rec_a, R, k,
                                                                         res.t, res.a);
     };
-    using Y = std::true_type;
-    using N = std::false_type;
     In ia, ib;
     Out ra, rb;
     if (!HAS_REW) {
 #pragma unroll
         for (int i = 0; i < 4 * P; ++i) ia.r[i] = ib.r[i] = 0.f;
     }
-    const int Q = tl >> 2;
-    load(ia, Q - 1);
-    if (Q == 1) {
-        if (first_chunk) body(ia, ra, ib, rb, 0, Y{}, N{}, N{});
-        else body(ia, ra, ib, rb, 0, N{}, N{}, N{});
-        store(ra, 0);
-        return;
-    }
-    if (first_chunk) body(ia, ra, ib, rb, Q - 1, Y{}, N{}, Y{});
-    else body(ia, ra, ib, rb, Q - 1, N{}, N{}, Y{});
-    int q = Q - 2;
-    for (; q >= 2; q -= 2) {
-        body(ib, rb, ia, ra, q, N{}, Y{}, Y{});
-        body(ia, ra, ib, rb, q - 1, N{}, Y{}, Y{});
-    }
-    if (q == 1) {
-        body(ib, rb, ia, ra, 1, N{}, Y{}, Y{});
-        body(ia, ra, ib, rb, 0, N{}, Y{}, N{});
-        store(ra, 0);
-    } else {
-        body(ib, rb, ia, ra, 0, N{}, Y{}, N{});
-        store(rb, 0);
-    }
+    pinned_order_groups(tl >> 2, first_chunk, ia, ib, ra, rb, load, store, body);
 }
 
 // ns = ring depth (2..4 stages): 2 when the grid fills the SMs (more resident warps hide the latency better than
@@ -641,7 +735,6 @@ __global__ void __launch_bounds__(96) k_target_rows_ws(const ScanParams k, int c
         const float R = active ? k.boot[(int64_t)(b0 + r) * k.boot_sb + (int64_t)p * k.boot_sp] : 0.f;
         Rec<MT> rec_t;
         Rec<MA> rec_a;
-        struct Grp { float v[4], r[4], rho[4], c[4]; };
         int slot = 0;
         uint32_t par = 0;
         for (int i = 0; i < n; ++i) {
@@ -654,70 +747,8 @@ __global__ void __launch_bounds__(96) k_target_rows_ws(const ScanParams k, int c
                 float* pr = st + TR * RSV + r * RSV + p;
                 const float* prho = st + 2 * TR * RSV + r * RSR + (RHO_PP ? p : 0);
                 const float* pc = prho + TR * RSR;
-                auto load_group = [&](Grp& g, int q) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        g.v[j] = pv[(q * 4 + j) * P];
-                        if (HAS_REW) g.r[j] = pr[(q * 4 + j) * P];
-                    }
-                    if (NEED_RHO) {
-                        if (WR == 1) {   // rho / c broadcast over players: 4 steps are one 16-byte unit
-                            const float4 a = *reinterpret_cast<const float4*>(prho + q * 4);
-                            g.rho[0] = a.x; g.rho[1] = a.y; g.rho[2] = a.z; g.rho[3] = a.w;
-                            if (!c_alias) {
-                                const float4 b = *reinterpret_cast<const float4*>(pc + q * 4);
-                                g.c[0] = b.x; g.c[1] = b.y; g.c[2] = b.z; g.c[3] = b.w;
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                g.rho[j] = prho[(q * 4 + j) * WR];
-                                if (!c_alias) g.c[j] = pc[(q * 4 + j) * WR];
-                            }
-                        }
-                    }
-                };
-                auto compute_group = [&](const Grp& g, int q, auto first_tag) {
-                    constexpr bool FIRST = decltype(first_tag)::value;
-#pragma unroll
-                    for (int j = 3; j >= 0; --j) {
-                        const float r_ = HAS_REW ? g.r[j] : 0.f;
-                        const float rh = NEED_RHO ? g.rho[j] : 0.f;
-                        const float c_ = NEED_RHO ? (c_alias ? g.rho[j] : g.c[j]) : 0.f;
-                        float t1, a1, t2, a2;
-                        if (FIRST && j == 3) {
-                            rec_t.first(g.v[j], r_, rh, c_, R, k, t1, a1);
-                            if (MT != MA) {
-                                rec_a.first(g.v[j], r_, rh, c_, R, k, t2, a2);
-                                a1 = a2;
-                            }
-                        } else {
-                            rec_t.next(g.v[j], r_, rh, c_, k, t1, a1);
-                            if (MT != MA) {
-                                rec_a.next(g.v[j], r_, rh, c_, k, t2, a2);
-                                a1 = a2;
-                            }
-                        }
-                        pv[(q * 4 + j) * P] = a1;
-                        pr[(q * 4 + j) * P] = t1;
-                    }
-                };
-                Grp ga, gb;
-                int q = (tl >> 2) - 1;
-                load_group(ga, q);
-                if (i == 0) {
-                    if (q >= 1) load_group(gb, q - 1);
-                    compute_group(ga, q, std::true_type{});
-                    --q;
-                    if (q >= 0) ga = gb;
-                }
-                for (; q >= 1; q -= 2) {
-                    load_group(gb, q - 1);
-                    compute_group(ga, q, std::false_type{});
-                    if (q >= 2) load_group(ga, q - 2);
-                    compute_group(gb, q - 1, std::false_type{});
-                }
-                if (q == 0) compute_group(ga, 0, std::false_type{});
+                scan_chunk_seqlane_v2<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP>(pv, pr, prho, pc, c_alias != 0, tl, i == 0,
+                                                                            rec_t, rec_a, R, k);
             }
             mbar_arrive(done + slot);
             if (++slot == ns) {
@@ -857,15 +888,17 @@ inline int ws_row_bytes(int B) {
     return B >= wide ? 512 : 256;
 }
 
-// Which lane mapping the warp-specialised kernel uses by default (measured: profiles/r2_target_ws_rowlane.md).
-// Row per lane pays where the compute warp is the critical path: few tiles and long rows.  1024 x 4,096, fraction of the
-// HBM peak, sequence per lane -> row per lane: TD 0.68 -> 0.76 (value head) / 0.79 -> 0.89 (return head), UPGO
-// 0.61 -> 0.69 / 0.73 -> 0.72, V-Trace 0.62 -> 0.66 / 0.67 -> 0.75, V-Trace + UPGO 0.53 -> 0.58 / 0.61 -> 0.68 (the
-// V-Trace and TD-with-rewards numbers need the pinned-order scan, scan_chunk_rowlane_v2); T = 512 / 2048 and B = 8,192
-// gain the same 5-20 %.  At T = 200, at B >= 16,384 and at B = 2,048 (64 tiles) it is neutral or slower.
-inline bool ws_rowlane_default(int B, int T, bool need_rho) {
-    (void)need_rho;
-    return T >= 512 && B > 2048 && B <= 8192;
+// Which lane mapping the warp-specialised kernel uses by default (measured: profiles/r2_target_ws_rowlane.md, section 7;
+// both mappings run their pinned-order scans).  Row per lane (32-row tiles) pays where the compute warp is the critical
+// path, i.e. few tiles and long rows.  Fraction of the HBM peak, sequence per lane | row per lane, return / value head:
+//   1024 x 4,096: TD 0.81 / 0.71 | 0.89 / 0.76, UPGO 0.75 / 0.62 | 0.72 / 0.70, V-Trace 0.78 / 0.70 | 0.76 / 0.66,
+//                 V-Trace + UPGO 0.74 / 0.65 | 0.69 / 0.57     (same pattern at T = 512 and 2048)
+//   1024 x 8,192: every mode 0.73-0.77 | 0.77-0.81           (same at T = 512 and 2048)
+// At T = 200, at B >= 16,384 and at B <= 2,048 row per lane is neutral or slower.
+inline bool ws_rowlane_default(int B, int T, bool need_rho, bool upgo_with_rewards) {
+    if (T < 512 || B <= 2048 || B > 8192) return false;
+    if (B >= 6144) return true;
+    return !need_rho && !upgo_with_rewards;
 }
 
 // long rows: the warp-specialised kernel (16-row tiles at P = 2); rows of <= 64 steps: one warp per 32 x 16 tile
@@ -874,7 +907,8 @@ int launch_rows(const ScanParams& k, cudaStream_t st) {
     if (k.T > B200RL_SHORT_T) {
         // knob target_ws_rowlane = 0 / 1: lane = (row, player) with 32/P-row tiles / lane = row with 32-row tiles
         long long rl = 0;
-        const bool rowlane = P > 1 && (b200rl_tuning(B200RL_TUNE_TARGET_WS_ROWLANE, &rl) ? rl != 0 : ws_rowlane_default(k.B, k.T, NEED_RHO));
+        const bool rowlane = P > 1 && (b200rl_tuning(B200RL_TUNE_TARGET_WS_ROWLANE, &rl) ? rl != 0 : ws_rowlane_default(k.B, k.T, NEED_RHO,
+                                                      HAS_REW && (MT == B200RL_TARGET_UPGO || MA == B200RL_TARGET_UPGO)));
         if (rowlane) {
             if (ws_row_bytes(k.B) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P, true>(k, st);
             return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P, true>(k, st);
