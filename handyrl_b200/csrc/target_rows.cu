@@ -877,13 +877,16 @@ int launch_ws(const ScanParams& k, cudaStream_t st) {
     return b200rl_check_launch("k_target_rows_ws");
 }
 
-// Chunk width of the warp-specialised kernel: 256 B per row and fetch up to B200RL_TARGET_WS_WIDE_ROWS batch rows
-// (more chunks in flight per CTA while few CTAs share an SM), 512 B beyond (measured at B = 65,536: +3-9 % at
-// T = 200, +2-4 % at T = 1024; at B = 16,384 and T = 200 the wide chunks are 15 % slower).
+// Chunk width of the warp-specialised kernel: 256 B per row and fetch (32 timesteps at P = 2) or 512 B (64 timesteps).
+// Wide chunks halve the chunk hand-offs per row and pay at both ends: from B200RL_TARGET_WS_WIDE_ROWS batch rows up
+// (measured at B = 65,536: +3-9 % at T = 200, +2-4 % at T = 1024) and for few tiles - B <= 2,048: +4-13 % on all 24
+// cells of T in {200, 512, 1024}; the head without rewards at B = 4,096: +0-5 % on 11 of 12 cells (with rewards it is
+// mixed, -3 to +2 %).  In between they lose: B = 8,192 value head up to -14 %, B = 16,384 and T = 200 -15 %.
 // Knob target_ws_row = 256 / 512 forces either (b200rl_set_tuning, so that a test can cover both in one process).
-inline int ws_row_bytes(int B) {
+inline int ws_row_bytes(int B, bool has_rew) {
     long long v = 0;
     if (b200rl_tuning(B200RL_TUNE_TARGET_WS_ROW, &v)) return v >= 512 ? 512 : 256;
+    if (B <= 2048 || (B < 6144 && !has_rew)) return 512;
     const long long wide = b200rl_tuning(B200RL_TUNE_TARGET_WS_WIDE_ROWS, &v) ? v : 32768;
     return B >= wide ? 512 : 256;
 }
@@ -910,10 +913,10 @@ int launch_rows(const ScanParams& k, cudaStream_t st) {
         const bool rowlane = P > 1 && (b200rl_tuning(B200RL_TUNE_TARGET_WS_ROWLANE, &rl) ? rl != 0 : ws_rowlane_default(k.B, k.T, NEED_RHO,
                                                       HAS_REW && (MT == B200RL_TARGET_UPGO || MA == B200RL_TARGET_UPGO)));
         if (rowlane) {
-            if (ws_row_bytes(k.B) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P, true>(k, st);
+            if (ws_row_bytes(k.B, HAS_REW) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P, true>(k, st);
             return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P, true>(k, st);
         }
-        if (ws_row_bytes(k.B) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P, false>(k, st);
+        if (ws_row_bytes(k.B, HAS_REW) == 512) return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 128 / P, false>(k, st);
         return launch_ws<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 64 / P, false>(k, st);
     }
     return launch_shape<MT, MA, P, HAS_REW, NEED_RHO, RHO_PP, 32, 16>(k, st);
