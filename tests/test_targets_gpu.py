@@ -92,14 +92,17 @@ def test_cs_is_rhos_same_tensor(B, T, P, rpp, vt, pt):
 
 
 @pytest.mark.parametrize("B,T,P,rpp", [(1000, 200, 2, False), (257, 128, 2, True), (333, 128, 1, False),
-                                       (4096, 1024, 2, False), (17, 68, 2, False)])
+                                       (4096, 1024, 2, False), (17, 68, 2, False), (19, 76, 2, False),
+                                       (33, 84, 2, True)])
 @pytest.mark.parametrize("vt,pt", [('TD', 'TD'), ('UPGO', 'UPGO'), ('VTRACE', 'VTRACE'), ('VTRACE', 'UPGO'),
                                    ('UPGO', 'VTRACE'), ('TD', 'UPGO')])
 @pytest.mark.parametrize("head", ['value', 'return'])
 def test_long_rows_ws_kernel(monkeypatch, B, T, P, rpp, vt, pt, head):
     """Rows longer than 64 steps run in the warp-specialised kernel (loader / compute / storer warps, mbarrier
     ring).  Both chunk widths and several ring depths must give the oracle's bits, with ragged last tiles, a
-    partial first chunk (T % chunk != 0), per-player rhos, P = 1 and cs aliasing rhos."""
+    partial first chunk (T % chunk != 0), per-player rhos, P = 1 and cs aliasing rhos.  The pinned-order scans work on
+    groups of four timesteps, two per loop trip: first chunks of 1 (T = 68), 2 (T = 200), 3 (T = 76) and 5 (T = 84)
+    groups cover their single-group, even and odd paths, full chunks the steady loop."""
     from handyrl_b200 import _lib
     from handyrl_b200.losses import compute_target_pair
     d = target_inputs(B, T, P, head, rpp, seed=B + T + 7)
